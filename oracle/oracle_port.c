@@ -1,0 +1,311 @@
+/*
+ * oracle_port.c - CPU restatement of the reference ray caster. TEST INFRASTRUCTURE ONLY.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this.
+ * The product path (libvr5.so) never links or calls it and has no CPU fallback.
+ *
+ * Parity status: PINNED. This restatement is checked bit-for-bit against the reference's own CPURenderer
+ * (compiled unmodified into oracle/_ref/libvolr_ref.so by oracle/Makefile) on Bucky.pvm and on synthetic
+ * volumes by tests/test_oracle_pin.py (where /root/reference exists), and against the committed golden
+ * fixtures those runs produced (tests/golden/, made by tests/golden/make_golden.py).
+ *
+ * Build rules: -O2 -ffp-contract=off, never -march=native / -mfma / -ffast-math. x86-64 SSE
+ * fp32 is then strict IEEE-754 single precision with one rounding per operation, which is what every
+ * expression below relies on. Each fp32 operation is written as its own statement so that the evaluation
+ * order of the reference expression it restates is explicit.
+ *
+ * Documented deviation: voxel indices are computed in 64 bit. The reference uses 32-bit unsigned
+ * arithmetic (ModelBase.h:18-22), identical for every volume below 2^32 voxels.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/vr5_pod.h"
+
+typedef struct orc_counters {
+    uint64_t rays_hit;   /* rays for which intersect() returned true */
+    uint64_t rays_accum; /* rays that entered the accumulation loop (and therefore wrote a pixel) */
+    uint64_t esl_iters;  /* iterations of the empty-space loop that leapt */
+    uint64_t samples;    /* iterations of the accumulation loop = classified voxel fetches (the bench unit) */
+    uint64_t shaded;     /* samples that took the shading path (second voxel fetch) */
+} orc_counters;
+
+/* common.h:93-101 - ternary semantics (NaN and signed-zero behaviour differ from fminf/fmaxf) */
+static inline float sel_min(float a, float b) { return a < b ? a : b; }
+static inline float sel_max(float a, float b) { return a > b ? a : b; }
+
+/* common.h:105-110 map_float_int: truncate f*n toward zero, clamp to [0, n-1] */
+static inline uint32_t unit_to_index(float f, uint32_t n) {
+    float scaled = f * (float)n;
+    long i = (long)scaled;
+    if (i >= (long)(int)n) i = (long)n - 1;
+    if (i < 0) i = 0;
+    return (uint32_t)i;
+}
+
+/* the (p + 1) * 0.5f world -> unit-cube mapping used by ModelBase.h:19-21 and RaycasterBase.h:57-62, 68-72 */
+static inline uint32_t world_to_voxel(float p, uint32_t n) {
+    float shifted = p + 1.0f;
+    float unit = shifted * 0.5f;
+    return unit_to_index(unit, n);
+}
+
+/* ModelBase.h:17-23 nearest-neighbour fetch (64-bit index: see header) */
+static inline uint8_t fetch_voxel(const vr5_model *m, float px, float py, float pz) {
+    uint64_t zi = world_to_voxel(pz, m->dims.z);
+    uint64_t yi = world_to_voxel(py, m->dims.y);
+    uint64_t xi = world_to_voxel(px, m->dims.x);
+    return m->data[zi * m->dims.x * m->dims.y + yi * m->dims.x + xi];
+}
+
+/* ViewBase.h:23-35 get_ray */
+static inline void primary_ray(const vr5_view *v, int col, int row, vr5_f3 *o, vr5_f3 *d) {
+    float cx = (float)(col - (int)v->dims.x / 2);
+    float cy = (float)(row - (int)v->dims.y / 2);
+    float rx = v->right_plane.x * cx, ry = v->right_plane.y * cx, rz = v->right_plane.z * cx;
+    float ux = v->up_plane.x * cy, uy = v->up_plane.y * cy, uz = v->up_plane.z * cy;
+    if (v->perspective) {
+        *o = v->origin;
+        float tx = v->direction.x + rx, ty = v->direction.y + ry, tz = v->direction.z + rz;
+        d->x = tx + ux; d->y = ty + uy; d->z = tz + uz;
+    } else {
+        *d = v->direction;
+        float tx = v->origin.x + rx, ty = v->origin.y + ry, tz = v->origin.z + rz;
+        o->x = tx + ux; o->y = ty + uy; o->z = tz + uz;
+    }
+}
+
+/* RaycasterBase.h:32-42 intersect: slab test against [min_bound, -min_bound]; zero components replaced on a copy */
+static inline int clip_ray(const vr5_model *m, vr5_f3 o, vr5_f3 d, float *k_near, float *k_far) {
+    if (d.x == 0) d.x = 0.00001f;
+    if (d.y == 0) d.y = 0.00001f;
+    if (d.z == 0) d.z = 0.00001f;
+    float lo_x = m->min_bound.x - o.x, lo_y = m->min_bound.y - o.y, lo_z = m->min_bound.z - o.z;
+    float hi_x = -m->min_bound.x - o.x, hi_y = -m->min_bound.y - o.y, hi_z = -m->min_bound.z - o.z;
+    float k1x = lo_x / d.x, k1y = lo_y / d.y, k1z = lo_z / d.z;
+    float k2x = hi_x / d.x, k2y = hi_y / d.y, k2z = hi_z / d.z;
+    float near = sel_max(sel_max(sel_min(k1x, k2x), sel_min(k1y, k2y)), sel_min(k1z, k2z));
+    float far = sel_min(sel_min(sel_max(k1x, k2x), sel_max(k1y, k2y)), sel_max(k1z, k2z));
+    near = sel_max(near, 0);
+    *k_near = near;
+    *k_far = far;
+    return (near < far) && (far > 0);
+}
+
+/* RaycasterBase.h:52-65 sample_data_esl: word = (zblk*32 + yblk), bit = xblk; set bit = empty block */
+static inline int block_is_empty(const vr5_raycaster *r, float px, float py, float pz) {
+    uint32_t bd = r->esl_block_dims;
+    uint16_t word = (uint16_t)((world_to_voxel(pz, r->volume.dims.z) / bd) * VR5_ESL_VOLUME_DIMS +
+                               (world_to_voxel(py, r->volume.dims.y) / bd));
+    uint32_t bits = r->esl_volume[word];
+    uint16_t bit = (uint16_t)(world_to_voxel(px, r->volume.dims.x) / bd);
+    return (bits & (1u << bit)) != 0;
+}
+
+/* RaycasterBase.h:67-85 leap_empty_space: distance to the nearest exit face of the current block, in whole steps */
+static inline float leap_distance(const vr5_raycaster *r, float px, float py, float pz, vr5_f3 d) {
+    uint32_t bd = r->esl_block_dims;
+    uint16_t bx = (uint16_t)(world_to_voxel(px, r->volume.dims.x) / bd);
+    uint16_t by = (uint16_t)(world_to_voxel(py, r->volume.dims.y) / bd);
+    uint16_t bz = (uint16_t)(world_to_voxel(pz, r->volume.dims.z) / bd);
+    if (d.x > 0) bx++;
+    if (d.y > 0) by++;
+    if (d.z > 0) bz++;
+    float fx = r->esl_block_size.x * (float)bx, fy = r->esl_block_size.y * (float)by, fz = r->esl_block_size.z * (float)bz;
+    float wx = r->volume.min_bound.x + fx, wy = r->volume.min_bound.y + fy, wz = r->volume.min_bound.z + fz;
+    float ex = wx - px, ey = wy - py, ez = wz - pz;
+    float kx = ex / d.x, ky = ey / d.y, kz = ez / d.z;
+    if (d.x == 0) kx = 100;
+    if (d.y == 0) ky = 100;
+    if (d.z == 0) kz = 100;
+    float dk = sel_min(kx, ky);
+    dk = sel_min(dk, kz);
+    dk = sel_max(dk, 0);
+    float q = dk / r->ray_step;
+    dk = floorf(q) * r->ray_step;
+    return dk;
+}
+
+/* RaycasterBase.h:87-98 shade (the caller has already applied the alpha / light_kd guard of CPURenderer.cpp:32) */
+static inline void shade_sample(const vr5_raycaster *r, vr5_f4 *c, float px, float py, float pz, uint8_t sample) {
+    float lx = r->view.light_pos.x - px, ly = r->view.light_pos.y - py, lz = r->view.light_pos.z - pz;
+    float xx = lx * lx, yy = ly * ly, zz = lz * lz;
+    float s = xx + yy;
+    s = s + zz;
+    float inv = 1.0f / sqrtf(s);
+    float nx = lx * inv, ny = ly * inv, nz = lz * inv;
+    float sample_l;
+    if (c->w > 0.05f && r->light_kd > 0.01f) {
+        float ox = nx * 0.01f, oy = ny * 0.01f, oz = nz * 0.01f;
+        float qx = px + ox, qy = py + oy, qz = pz + oz;
+        sample_l = (float)fetch_voxel(&r->volume, qx, qy, qz) / 255.0f;
+    } else {
+        sample_l = (float)sample / 255.0f;
+    }
+    float here = (float)sample / 255.0f;
+    float diff = sample_l - here;
+    diff = diff * r->light_kd;
+    c->x += diff;
+    c->y += diff;
+    c->z += diff;
+}
+
+/* CPURenderer.cpp:11-41 render_ray + RaycasterBase.h:44-50 write_color */
+static void cast_pixel(const vr5_raycaster *r, uint8_t *rgba8, int col, int row, orc_counters *cnt) {
+    vr5_f3 o, d;
+    float k, k_far;
+    primary_ray(&r->view, col, row, &o, &d);
+    if (!clip_ray(&r->volume, o, d, &k, &k_far)) return;
+    cnt->rays_hit++;
+    float px, py, pz;
+#define ADVANCE_POINT()                                   \
+    do {                                                  \
+        float mx = d.x * k, my = d.y * k, mz = d.z * k;   \
+        px = o.x + mx; py = o.y + my; pz = o.z + mz;      \
+    } while (0)
+    ADVANCE_POINT();
+    while (k <= k_far) { /* CPURenderer.cpp:18-25 leading empty-space loop */
+        if (r->esl && block_is_empty(r, px, py, pz)) {
+            k += leap_distance(r, px, py, pz, d);
+            cnt->esl_iters++;
+        } else {
+            break;
+        }
+        k += r->ray_step;
+        ADVANCE_POINT();
+    }
+    if (k > k_far) return;
+    cnt->rays_accum++;
+    vr5_f4 acc = {0, 0, 0, 0};
+    while (k <= k_far) { /* CPURenderer.cpp:29-39 accumulation loop */
+        uint8_t sample = fetch_voxel(&r->volume, px, py, pz);
+        vr5_f4 cur = r->transfer_fn[sample / VR5_TF_RATIO];
+        cnt->samples++;
+        if (cur.w > 0.05f && r->light_kd > 0.01f) {
+            shade_sample(r, &cur, px, py, pz, sample);
+            cnt->shaded++;
+        }
+        float t = 1 - acc.w;
+        float cx = cur.x * t, cy = cur.y * t, cz = cur.z * t, cw = cur.w * t;
+        acc.x = acc.x + cx; acc.y = acc.y + cy; acc.z = acc.z + cz; acc.w = acc.w + cw;
+        if (acc.w > r->ray_threshold) break;
+        k += r->ray_step;
+        ADVANCE_POINT();
+    }
+#undef ADVANCE_POINT
+    uint8_t *px8 = rgba8 + 4 * ((size_t)row * r->view.dims.x + (size_t)col);
+    px8[0] = (uint8_t)unit_to_index(acc.x, 256);
+    px8[1] = (uint8_t)unit_to_index(acc.y, 256);
+    px8[2] = (uint8_t)unit_to_index(acc.z, 256);
+    px8[3] = (uint8_t)unit_to_index(acc.w, 256);
+}
+
+/*
+ * CPURenderer.cpp:43-53 render_volume restricted to rows [row0, row1): clears those rows, casts one ray per
+ * pixel in row-major order. Returns 1 on a missing input like the reference, else 0. `cnt` may be NULL.
+ * Re-entrant: distinct row ranges may run on distinct threads.
+ */
+int orc_render_rows(const vr5_raycaster *r, uint8_t *rgba8, int row0, int row1, orc_counters *cnt) {
+    if (r->volume.data == NULL || r->transfer_fn == NULL || r->esl_volume == NULL || rgba8 == NULL) return 1;
+    orc_counters local = {0, 0, 0, 0, 0};
+    int w = r->view.dims.x, h = r->view.dims.y;
+    if (row0 < 0) row0 = 0;
+    if (row1 > h) row1 = h;
+    if (row1 > row0) memset(rgba8 + (size_t)row0 * w * 4, 0, (size_t)(row1 - row0) * w * 4);
+    for (int row = row0; row < row1; row++)
+        for (int col = 0; col < w; col++) cast_pixel(r, rgba8, col, row, &local);
+    if (cnt) *cnt = local;
+    return 0;
+}
+
+int orc_render(const vr5_raycaster *r, uint8_t *rgba8, orc_counters *cnt) {
+    return orc_render_rows(r, rgba8, 0, r->view.dims.y, cnt);
+}
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Scene builders restated (host side, once per change)
+ * ------------------------------------------------------------------------------------------------------- */
+
+/* RaycasterBase.cpp:76-84 reset_transfer_fn: R ramp for i<=42, G for 43..84, B above, alpha i/128 above 12.75 */
+void orc_default_base_tf(float *rgba128) {
+    const int third = VR5_TF_SIZE / 3;
+    for (int i = 0; i < VR5_TF_SIZE; i++) {
+        float *e = rgba128 + 4 * i;
+        e[0] = i <= third ? (float)(i * 3) / (float)VR5_TF_SIZE : 0.0f;
+        e[1] = (i > third && i <= third * 2) ? (float)((i - third) * 3) / (float)VR5_TF_SIZE : 0.0f;
+        e[2] = i > third * 2 ? (float)((i - third * 2) * 3) / (float)VR5_TF_SIZE : 0.0f;
+        e[3] = (float)i > ((255.0f * 0.1f) / (float)VR5_TF_RATIO) ? (float)i / (float)VR5_TF_SIZE : 0.0f;
+    }
+}
+
+/* RaycasterBase.cpp:46-52 pre-multiplication */
+void orc_premultiply_tf(const float *base128, float *out128) {
+    for (int i = 0; i < VR5_TF_SIZE; i++) {
+        float a = base128[4 * i + 3];
+        out128[4 * i + 0] = base128[4 * i + 0] * a;
+        out128[4 * i + 1] = base128[4 * i + 1] * a;
+        out128[4 * i + 2] = base128[4 * i + 2] * a;
+        out128[4 * i + 3] = a;
+    }
+}
+
+/* RaycasterBase.cpp:53-67: bit i set <=> no TF entry in [min/2, max/2] has non-zero alpha */
+void orc_build_esl_bits(const float *premult128, const uint8_t *minmax /* 32768 x {min,max} */, uint32_t *bits1024) {
+    uint16_t next_opaque[VR5_TF_SIZE];
+    for (int x = 0; x < VR5_TF_SIZE; x++) {
+        int y = x;
+        while (y < VR5_TF_SIZE && premult128[4 * y + 3] == 0) y++;
+        next_opaque[x] = (uint16_t)y;
+    }
+    memset(bits1024, 0, VR5_ESL_VOLUME_SIZE * sizeof(uint32_t));
+    for (uint32_t i = 0; i < 32768u; i++) {
+        uint8_t lo = minmax[2 * i], hi = minmax[2 * i + 1];
+        if (next_opaque[lo / VR5_TF_RATIO] > hi / VR5_TF_RATIO) bits1024[i / 32] |= 1u << (i % 32);
+    }
+}
+
+/* RaycasterBase.cpp:94-125 set_volume: ESL block edge, per-block min/max (64-bit index), block size in world units */
+void orc_build_minmax(const uint8_t *data, uint32_t dx, uint32_t dy, uint32_t dz, uint16_t *block_dims_out,
+                      uint8_t *minmax /* 32768 x 2 */, float *block_size3) {
+    uint32_t max_dim = dx > dy ? (dx > dz ? dx : dz) : (dy > dz ? dy : dz);
+    uint32_t bd = (max_dim + VR5_ESL_VOLUME_DIMS - 1) / VR5_ESL_VOLUME_DIMS;
+    if (bd < VR5_ESL_MIN_BLOCK_SIZE) bd = VR5_ESL_MIN_BLOCK_SIZE;
+    for (uint32_t i = 0; i < 32768u; i++) { minmax[2 * i] = 255; minmax[2 * i + 1] = 0; }
+    for (uint32_t z = 0; z < dz; z++)
+        for (uint32_t y = 0; y < dy; y++) {
+            const uint8_t *rowp = data + ((uint64_t)z * dy + y) * dx;
+            uint32_t base = (z / bd) * 1024u + (y / bd) * 32u;
+            for (uint32_t x = 0; x < dx; x++) {
+                uint8_t s = rowp[x];
+                uint8_t *mm = minmax + 2 * (base + x / bd);
+                if (mm[0] > s) mm[0] = s;
+                if (mm[1] < s) mm[1] = s;
+            }
+        }
+    *block_dims_out = (uint16_t)bd;
+    block_size3[0] = 2.0f * (float)bd / (float)dx;
+    block_size3[1] = 2.0f * (float)bd / (float)dy;
+    block_size3[2] = 2.0f * (float)bd / (float)dz;
+}
+
+/* RaycasterBase.cpp:86-92 reset_ray_step */
+float orc_default_ray_step(uint32_t max_dim) {
+    float step = 2.0f / (float)(int)max_dim;
+    step -= step / (float)(int)max_dim;
+    return step;
+}
+
+/* ModelBase.cpp:19-33 compute_histogram: 4th root of bin counts, normalised to the largest */
+void orc_histogram(const uint8_t *data, uint64_t n, float *hist256) {
+    uint32_t bins[256];
+    memset(bins, 0, sizeof(bins));
+    for (uint64_t i = 0; i < n; i++) bins[data[i]]++;
+    float top = 0;
+    for (int i = 0; i < 256; i++) {
+        hist256[i] = sqrtf(sqrtf((float)bins[i])); /* C++ float overloads of sqrt in the reference */
+        if (hist256[i] > top) top = hist256[i];
+    }
+    for (int i = 0; i < 256; i++) hist256[i] = hist256[i] / top;
+}
