@@ -1,0 +1,167 @@
+/*
+ * vr5.h - C ABI of the B200-native ray caster ("GPURenderer5"), the drop-in boundary for the one hot path
+ *         volume + transfer function + view parameters in  ->  RGBA8 framebuffer out.
+ *
+ * Every entry point replaces one piece of the reference's Renderer plugin interface (Renderer.h:13-28) as the
+ * reference's CUDA renderers implement it; the reference file:line each one stands in for is cited per function.
+ * Plain pointers and sizes only: no C++, CUDA or torch types. The C++ adaptor `class GPURenderer5 : public
+ * Renderer` (volume-rendering_b200/csrc/GPURenderer5.{h,cpp}) and the headless bench drivers (bench.py through
+ * ctypes, tools/volr_headless.cpp) are thin callers of this layer. See INTEGRATION.md for the binding a VolR
+ * maintainer adds.
+ *
+ * Conventions (reference cuda_utils.h:21-49, GPURenderer1.cu:86-112): functions return int, 0 = success,
+ * 1 = failure (missing input, allocation failure, CUDA error). The library never calls exit(); the message of the
+ * last failure is kept per handle (vr5_last_error). There is NO CPU fallback: without a CUDA device vr5_create fails.
+ *
+ * Threading: like the reference (single GLUT thread) a handle is not re-entrant. Rendering is blocking by default
+ * (the frame is complete when vr5_render returns); vr5_render_async + vr5_sync expose the stream for overlap.
+ */
+#ifndef VR5_H
+#define VR5_H
+
+#include "vr5_pod.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VR5_VERSION 1
+
+typedef struct vr5_renderer vr5_renderer; /* opaque; owns every device allocation it makes */
+
+/* Per-frame parameters: `Raycaster` (RaycasterBase.h:20-30) minus the three pointers, which the renderer owns as
+ * device copies (the reference overwrites them with device pointers in render_volume, GPURenderer1.cu:103-105). */
+typedef struct vr5_params {
+    vr5_view view;           /* ViewBase.h:14-21 */
+    float ray_step;          /* RaycasterBase.h:24 */
+    float ray_threshold;     /* RaycasterBase.h:25 */
+    uint32_t esl;            /* RaycasterBase.h:26 (bool) */
+    uint32_t esl_block_dims; /* RaycasterBase.h:28 */
+    vr5_f3 esl_block_size;   /* RaycasterBase.h:29 */
+    float light_kd;          /* RaycasterBase.h:30 */
+    vr5_f3 min_bound;        /* Model::min_bound (ModelBase.h:15); (-1,-1,-1) in every reference path */
+} vr5_params;
+
+/* Work counters of one frame (instrumented kernel variant; never the timed kernel). SURVEY 8(d). */
+typedef struct vr5_counters {
+    uint64_t rays_hit;   /* rays with a non-empty clip interval (intersect() true) */
+    uint64_t rays_accum; /* rays that entered the accumulation loop */
+    uint64_t esl_iters;  /* empty-space-leap iterations (CPURenderer.cpp:18-25) */
+    uint64_t samples;    /* accumulation-loop iterations = classified voxel fetches: the bench unit */
+    uint64_t shaded;     /* samples that took the shading path (second voxel fetch) */
+} vr5_counters;
+
+/* Voxel sampler policies (all nearest-neighbour, bit-identical results; they differ in memory path only). */
+enum { VR5_SAMPLER_LINEAR = 0,  /* x-fastest linear array, LDG.U8 (the reference's layout, ModelBase.h:18-22) */
+       VR5_SAMPLER_BRICK = 1,   /* 8x4x4-voxel bricks (one 128-B line each, 4x4x2 per 32-B sector), LDG.U8 */
+       VR5_SAMPLER_TEX3D = 2 }; /* cudaArray 3-D texture, integer-coordinate point fetch (TLD) */
+
+/* ---- lifecycle ------------------------------------------------------------------------------------------ */
+
+/* GPURenderer1 constructor minus the three set_* calls (GPURenderer1.cu:17-21) and cuda_init's device pick
+ * (VolR.cpp:128-198). `device` is a CUDA ordinal; -1 = current device. */
+int vr5_create(int device, vr5_renderer **out);
+/* ~GPURenderer1 / ~GPURenderer4 (GPURenderer1.cu:23-28, GPURenderer4.cu:24-31): frees all device state. */
+void vr5_destroy(vr5_renderer *r);
+/* Renderer::get_name (Renderer.h:16-18) */
+const char *vr5_name(void);
+/* message of the last failure on this handle ("" if none); with r == NULL, of the last failed vr5_create */
+const char *vr5_last_error(const vr5_renderer *r);
+int vr5_version(void);
+
+/* ---- scene state (host data in, device copies owned by the renderer) -------------------------------------- */
+
+/* Renderer::set_window_buffer(View) (GPURenderer1.cu:74-84): (re)allocates the internal framebuffer. */
+int vr5_set_window(vr5_renderer *r, uint16_t width, uint16_t height);
+/* Renderer::set_transfer_fn(Raycaster) (GPURenderer1.cu:65-72): uploads the 128 pre-multiplied RGBA entries AND the
+ * 1024-word ESL bitfield (both change together, RaycasterBase.cpp:46-74). */
+int vr5_set_transfer_fn(vr5_renderer *r, const float *tf_premult_rgba128, const uint32_t *esl_bits1024);
+/* Renderer::set_volume(Model) (GPURenderer1.cu:86-98; GPURenderer4.cu:114-143): uploads the x-fastest uint8 grid and
+ * builds the layout of the active sampler. `bytes` must equal dx*dy*dz (64 bit: SURVEY H3). 1 = no data / no memory. */
+int vr5_set_volume(vr5_renderer *r, const uint8_t *host_data, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz);
+/* Same, from a linear grid already in device memory (device generator, NCCL broadcast). The renderer copies it. */
+int vr5_set_volume_device(vr5_renderer *r, const uint8_t *dev_data, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz);
+/* Copies the linear grid back to the host (tests: hand the oracle the exact bytes the kernel sees). */
+int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes);
+/* Select VR5_SAMPLER_*; re-lays out the current volume if one is set. Default: VR5_SAMPLER_LINEAR or $VR5_SAMPLER. */
+int vr5_set_sampler(vr5_renderer *r, int sampler);
+int vr5_get_sampler(const vr5_renderer *r);
+
+/* ---- the hot path ----------------------------------------------------------------------------------------- */
+
+/* Renderer::render_volume(uchar4*, Raycaster) (GPURenderer1.cu:100-112, GPURenderer23.cu:60-81). Writes width*height
+ * RGBA8 pixels, row 0 first (RaycasterBase.h:44-50); every pixel is written (misses as 0), so no separate clear pass.
+ * out_is_device: 0 = host pointer (D2H copy inside, as renderers 1-2), 1 = device pointer (rendered in place, as
+ * renderers 3-4 into the mapped PBO, VolR.cpp:76-87), -1 = detect with cudaPointerGetAttributes. Blocking.
+ * The view dims must match vr5_set_window. */
+int vr5_render(vr5_renderer *r, const vr5_params *p, void *out_rgba8, int out_is_device);
+/* Same call taking the reference's 160-byte POD as is (its three pointers are ignored, GPURenderer1.cu:103-105). */
+int vr5_render_raycaster(vr5_renderer *r, const vr5_raycaster *rc, void *out_rgba8, int out_is_device);
+/* Non-blocking variant for device buffers (or pinned host buffers): enqueue on the renderer's stream and return. */
+int vr5_render_async(vr5_renderer *r, const vr5_params *p, void *out_rgba8, int out_is_device);
+/* cudaStreamSynchronize on the renderer's stream. */
+int vr5_sync(vr5_renderer *r);
+/* Use an external stream (a cudaStream_t passed as void*, e.g. torch's current stream); NULL restores the own stream. */
+int vr5_set_stream(vr5_renderer *r, void *cuda_stream);
+
+/* ---- measurement extras (headless bench driver; replace Profiler.cpp:46-78) -------------------------------- */
+
+/* Render `n_frames` frames back to back into a device buffer, timing EACH kernel launch with CUDA events on the
+ * launching stream; ms_out[n_frames]. l2_flush != 0 writes a >L2-sized scratch buffer between frames (untimed). */
+int vr5_render_timed(vr5_renderer *r, const vr5_params *frames, int n_frames, void *out_dev_rgba8, int l2_flush, float *ms_out);
+/* Run the instrumented variant of the kernel on one frame and return its work counters (no framebuffer needed). */
+int vr5_count(vr5_renderer *r, const vr5_params *p, vr5_counters *out);
+/* Number of kernels this handle has launched so far (render, count, layout, synth). */
+uint64_t vr5_launch_count(const vr5_renderer *r);
+/* Pinned host memory for the end-to-end path (cudaHostAlloc / cudaFreeHost). */
+void *vr5_host_alloc(uint64_t bytes);
+void vr5_host_free(void *p);
+/* Device scratch owned by the caller (plain cudaMalloc/cudaFree on the renderer's device). */
+void *vr5_device_alloc(vr5_renderer *r, uint64_t bytes);
+void vr5_device_free(vr5_renderer *r, void *p);
+int vr5_memcpy_d2h(vr5_renderer *r, void *host_dst, const void *dev_src, uint64_t bytes);
+
+/* ---- image-space partition for multi-GPU (the reference is single-GPU) ------------------------ */
+
+/* Rank `rank` of `world` renders the 4-row strips s with s % world == rank (interleaved for load balance).
+ * packed = 0: pixels go to their place in a full width*height frame (other ranks' rows untouched);
+ * packed = 1: the rank's strips are stored contiguously, strip j of the rank at row 4*j (vr5_strip_rows rows). */
+int vr5_set_partition(vr5_renderer *r, int rank, int world, int packed);
+/* rows of a packed strip buffer for (height, rank, world): 4 * number of strips owned (last strip may be short) */
+uint32_t vr5_strip_rows(uint16_t height, int rank, int world);
+/* On the gathering rank: scatter `world` packed strip buffers (concatenated, each padded to `rows_padded` rows) into
+ * a full frame. Both pointers are device pointers. */
+int vr5_unpack_strips(vr5_renderer *r, const void *packed_all, uint32_t rows_padded, int world, void *frame_rgba8);
+
+/* ---- synthetic volumes generated on the device (bench inputs) ------------------------------- */
+
+/* kind 0 = synthA (dense Marschner-Lobb-like), 1 = synthB (sparse spheres); integer arithmetic, byte-identical to
+ * the host generator the oracle uses (oracle/synth_volume.c). Result becomes the renderer's current volume. */
+int vr5_synth_volume(vr5_renderer *r, int kind, uint16_t n, uint32_t seed);
+
+/* ---- scene builders (host side, once per change): what RaycasterBase / ViewBase manufacture ----------------- */
+
+/* RaycasterBase::reset_transfer_fn default ramp (RaycasterBase.cpp:76-84): base (non pre-multiplied) 128 x RGBA */
+void vr5_scene_default_base_tf(float *base_rgba128);
+/* RaycasterBase::update_transfer_fn part 1 (RaycasterBase.cpp:46-52) */
+void vr5_scene_premultiply_tf(const float *base_rgba128, float *premult_rgba128);
+/* RaycasterBase::set_volume (RaycasterBase.cpp:94-125): ESL block edge, 32^3 x {min,max}, block size in world units */
+void vr5_scene_build_minmax(const uint8_t *data, uint16_t dx, uint16_t dy, uint16_t dz, uint16_t *esl_block_dims,
+                            uint8_t *minmax_32768x2, vr5_f3 *esl_block_size);
+/* RaycasterBase::update_transfer_fn part 2 (RaycasterBase.cpp:53-67) */
+void vr5_scene_build_esl_bits(const float *premult_rgba128, const uint8_t *minmax_32768x2, uint32_t *esl_bits1024);
+/* RaycasterBase::reset_ray_step (RaycasterBase.cpp:86-92) */
+float vr5_scene_default_ray_step(uint16_t dx, uint16_t dy, uint16_t dz);
+/* ViewBase::set_viewport_dims + toggle_perspective(1) + set_camera_position (ViewBase.cpp:49-113, VolR.cpp:232-247)
+ * with an own matrix stack instead of the GL one; light at its default (0,0,3). */
+void vr5_scene_camera(uint16_t width, uint16_t height, int perspective, float ax_deg, float ay_deg, float az_deg,
+                      float distance, vr5_view *out);
+/* Same as vr5_scene_build_minmax but computed on the device from the renderer's current volume */
+int vr5_build_minmax_device(vr5_renderer *r, uint16_t *esl_block_dims, uint8_t *minmax_32768x2, vr5_f3 *esl_block_size);
+/* ModelBase::compute_histogram (ModelBase.cpp:19-33) on the device from the current volume: 256 normalised bins */
+int vr5_histogram_device(vr5_renderer *r, float *hist256);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VR5_H */

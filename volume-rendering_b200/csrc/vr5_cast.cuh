@@ -1,0 +1,261 @@
+// vr5_cast.cuh - device side of the B200 ray caster: one ray per lane, 8x4-pixel warp tiles pulled from an atomic
+// tile queue by persistent warps, transfer-function LUT and ESL bitfield staged in shared memory.
+//
+// Parity rule: every fp32 operation the reference's CPURenderer performs is
+// performed here in the same order with the same IEEE-754 round-to-nearest result. All arithmetic goes through the
+// __f*_rn intrinsics below, which nvcc never contracts into FMA (the TU is also built with -fmad=false), division
+// and square root are the correctly rounded variants, denormals are kept (-ftz=false), min/max are the reference's
+// ternaries (common.h:93-101), float->index is truncation (common.h:105-110). Integer index arithmetic is free to
+// differ (layouts, 64-bit offsets) because it is exact.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace vr5 {
+
+constexpr int kCtaThreads = 256;  // 8 warps; each warp owns one 8x4 pixel tile at a time
+constexpr int kTileW = 8;
+constexpr int kTileH = 4;         // = strip height of the multi-GPU partition
+constexpr int kGroupTilesX = 4;   // queue order: groups of 4x8 tiles (32x32 px) so neighbouring queue slots
+constexpr int kGroupTilesY = 8;   //              touch neighbouring voxels (L1/L2 locality)
+
+struct Counters {
+    unsigned long long rays_hit, rays_accum, esl_iters, samples, shaded;
+};
+
+struct KArgs {
+    // view (ViewBase.h:14-21)
+    float ox, oy, oz;        // origin
+    float dx, dy, dz;        // direction
+    float rx, ry, rz;        // right_plane
+    float ux, uy, uz;        // up_plane
+    float lx, ly, lz;        // light_pos
+    int width, height;
+    int half_w, half_h;      // dims / 2 (integer halves, ViewBase.h:26-27)
+    int perspective;
+    // volume (ModelBase.h:11-16)
+    const uint8_t *vol;      // linear or bricked grid
+    cudaTextureObject_t tex; // 3-D texture (VR5_SAMPLER_TEX3D)
+    uint32_t nx1, ny1, nz1;  // dims - 1 (index clamp)
+    float hx, hy, hz;        // dims * 0.5f: (p + 1) * 0.5f * n == (p + 1) * (0.5f * n) exactly (power-of-two scaling)
+    uint32_t sx;             // linear: row stride; brick: bricks per row
+    uint64_t sxy;            // linear: slice stride; brick: bricks per slab
+    float mbx, mby, mbz;     // min_bound
+    // march (RaycasterBase.h:24-30)
+    float step, threshold;
+    float shade_alpha;       // 0.05f when light_kd > 0.01f else +inf: folds the uniform half of CPURenderer.cpp:32
+    float kd;
+    int esl;
+    uint32_t bd_magic;       // ceil(2^32 / esl_block_dims): exact idx / bd for idx < 2^16 via umulhi
+    uint32_t bd_is_one;
+    float bsx, bsy, bsz;     // esl_block_size
+    // tables
+    const float4 *tf;        // 128 pre-multiplied entries
+    const uint32_t *esl_bits;// 1024 words
+    // output
+    uchar4 *out;
+    int packed;              // 1: strips of this rank stored contiguously
+    int rank, world;
+    // tile queue
+    unsigned *queue;         // this frame's counter
+    unsigned *queue_next;    // zeroed by this frame for the next one
+    uint32_t n_queue;        // padded tile count
+    uint32_t tiles_x, tile_rows_local, groups_x;
+    Counters *counters;
+};
+
+// ---- exact fp32 helpers ----------------------------------------------------------------------------------
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float sel_min(float a, float b) { return a < b ? a : b; }  // common.h:93-96
+__device__ __forceinline__ float sel_max(float a, float b) { return a > b ? a : b; }  // common.h:98-101
+
+// common.h:105-110 map_float_int on an already scaled value: trunc toward zero, clamp to [0, n-1].
+// cvt.rzi.u32.f32 saturates: negatives and NaN -> 0, >= 2^32 -> 0xffffffff -> n-1. Matches the x86 (long) cast for
+// every |v| < 2^63 (beyond that, and for +inf, x86 yields LONG_MIN -> 0; unreachable for finite scenes).
+__device__ __forceinline__ uint32_t trunc_clamp(float v, uint32_t n_minus_1) { return min(__float2uint_rz(v), n_minus_1); }
+
+// (p + 1) * 0.5f * n with the two scalings merged (exact, see KArgs::hx)
+__device__ __forceinline__ uint32_t world_to_voxel(float p, float half_n, uint32_t n_minus_1) {
+    return trunc_clamp(fmul(fadd(p, 1.0f), half_n), n_minus_1);
+}
+
+// ---- voxel samplers (ModelBase.h:17-23; nearest neighbour, identical bytes on every path) ---------------------
+template <int SAMPLER>
+__device__ __forceinline__ uint32_t fetch_voxel(const KArgs &a, uint32_t ix, uint32_t iy, uint32_t iz);
+
+template <>
+__device__ __forceinline__ uint32_t fetch_voxel<0>(const KArgs &a, uint32_t ix, uint32_t iy, uint32_t iz) {
+    return __ldg(a.vol + ((uint64_t)iz * a.sxy + (iy * a.sx + ix)));
+}
+
+// 8x4x4 bricks: byte offset inside a brick = x0 x1 | y0 y1 | z0 || x2 | z1  (32-B sector = 4x4x2 voxels)
+template <>
+__device__ __forceinline__ uint32_t fetch_voxel<1>(const KArgs &a, uint32_t ix, uint32_t iy, uint32_t iz) {
+    uint32_t inner = (ix & 3u) | ((iy & 3u) << 2) | ((iz & 1u) << 4) | ((ix & 4u) << 3) | ((iz & 2u) << 5);
+    uint64_t brick = (uint64_t)(iz >> 2) * a.sxy + ((iy >> 2) * a.sx + (ix >> 3));
+    return __ldg(a.vol + (brick * 128u + inner));
+}
+
+template <>
+__device__ __forceinline__ uint32_t fetch_voxel<2>(const KArgs &a, uint32_t ix, uint32_t iy, uint32_t iz) {
+    uint32_t r0, r1, r2, r3;
+    asm("tex.3d.v4.u32.s32 {%0, %1, %2, %3}, [%4, {%5, %6, %7, %8}];"
+        : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+        : "l"(a.tex), "r"(ix), "r"(iy), "r"(iz), "r"(0));
+    return r0;
+}
+
+template <int SAMPLER>
+__device__ __forceinline__ uint32_t sample_volume(const KArgs &a, float px, float py, float pz) {
+    uint32_t iz = world_to_voxel(pz, a.hz, a.nz1);
+    uint32_t iy = world_to_voxel(py, a.hy, a.ny1);
+    uint32_t ix = world_to_voxel(px, a.hx, a.nx1);
+    return fetch_voxel<SAMPLER>(a, ix, iy, iz);
+}
+
+__device__ __forceinline__ uint32_t div_block(const KArgs &a, uint32_t idx) {
+    return a.bd_is_one ? idx : __umulhi(idx, a.bd_magic);
+}
+
+// ---- one ray (CPURenderer.cpp:11-41). Returns the packed RGBA8 pixel; 0 when the reference leaves it cleared. ----
+template <int SAMPLER, bool COUNT>
+__device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const float4 *lut, const uint32_t *esl_bits, int col, int row,
+                                             Counters &cnt) {
+    // View::get_ray (ViewBase.h:23-35)
+    const float cx = (float)(col - a.half_w);
+    const float cy = (float)(row - a.half_h);
+    float ox, oy, oz, dx, dy, dz;
+    if (a.perspective) {
+        ox = a.ox; oy = a.oy; oz = a.oz;
+        dx = fadd(fadd(a.dx, fmul(a.rx, cx)), fmul(a.ux, cy));
+        dy = fadd(fadd(a.dy, fmul(a.ry, cx)), fmul(a.uy, cy));
+        dz = fadd(fadd(a.dz, fmul(a.rz, cx)), fmul(a.uz, cy));
+    } else {
+        dx = a.dx; dy = a.dy; dz = a.dz;
+        ox = fadd(fadd(a.ox, fmul(a.rx, cx)), fmul(a.ux, cy));
+        oy = fadd(fadd(a.oy, fmul(a.ry, cx)), fmul(a.uy, cy));
+        oz = fadd(fadd(a.oz, fmul(a.rz, cx)), fmul(a.uz, cy));
+    }
+    // Raycaster::intersect (RaycasterBase.h:32-42); the zero fix-up applies to a local copy only
+    float k, k_far;
+    {
+        const float ex = dx == 0.0f ? 0.00001f : dx;
+        const float ey = dy == 0.0f ? 0.00001f : dy;
+        const float ez = dz == 0.0f ? 0.00001f : dz;
+        const float k1x = fdiv(fsub(a.mbx, ox), ex), k1y = fdiv(fsub(a.mby, oy), ey), k1z = fdiv(fsub(a.mbz, oz), ez);
+        const float k2x = fdiv(fsub(-a.mbx, ox), ex), k2y = fdiv(fsub(-a.mby, oy), ey), k2z = fdiv(fsub(-a.mbz, oz), ez);
+        k = sel_max(sel_max(sel_min(k1x, k2x), sel_min(k1y, k2y)), sel_min(k1z, k2z));
+        k_far = sel_min(sel_min(sel_max(k1x, k2x), sel_max(k1y, k2y)), sel_max(k1z, k2z));
+        k = sel_max(k, 0.0f);
+        if (!((k < k_far) && (k_far > 0.0f))) return 0u;
+    }
+    if (COUNT) cnt.rays_hit++;
+    float px = fadd(ox, fmul(dx, k)), py = fadd(oy, fmul(dy, k)), pz = fadd(oz, fmul(dz, k));
+
+    // leading empty-space loop (CPURenderer.cpp:18-25; sample_data_esl RaycasterBase.h:52-65; leap RaycasterBase.h:67-85)
+    if (a.esl) {
+        while (k <= k_far) {
+            uint32_t bx = div_block(a, world_to_voxel(px, a.hx, a.nx1));
+            uint32_t by = div_block(a, world_to_voxel(py, a.hy, a.ny1));
+            uint32_t bz = div_block(a, world_to_voxel(pz, a.hz, a.nz1));
+            const uint32_t word = esl_bits[(bz * 32u + by) & 1023u];
+            if (((word >> (bx & 31u)) & 1u) == 0u) break;
+            if (dx > 0.0f) bx++;
+            if (dy > 0.0f) by++;
+            if (dz > 0.0f) bz++;
+            float kx = fdiv(fsub(fadd(a.mbx, fmul(a.bsx, (float)bx)), px), dx);
+            float ky = fdiv(fsub(fadd(a.mby, fmul(a.bsy, (float)by)), py), dy);
+            float kz = fdiv(fsub(fadd(a.mbz, fmul(a.bsz, (float)bz)), pz), dz);
+            if (dx == 0.0f) kx = 100.0f;
+            if (dy == 0.0f) ky = 100.0f;
+            if (dz == 0.0f) kz = 100.0f;
+            float dk = sel_min(kx, ky);
+            dk = sel_min(dk, kz);
+            dk = sel_max(dk, 0.0f);
+            dk = fmul(floorf(fdiv(dk, a.step)), a.step);
+            k = fadd(k, dk);
+            if (COUNT) cnt.esl_iters++;
+            k = fadd(k, a.step);
+            px = fadd(ox, fmul(dx, k)); py = fadd(oy, fmul(dy, k)); pz = fadd(oz, fmul(dz, k));
+        }
+        if (k > k_far) return 0u;
+    }
+    if (COUNT) cnt.rays_accum++;
+
+    // accumulation loop (CPURenderer.cpp:28-39)
+    float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
+    while (k <= k_far) {
+        const uint32_t s = sample_volume<SAMPLER>(a, px, py, pz);
+        float4 c = lut[s];  // lut[s] == transfer_fn[s / TF_RATIO]
+        if (COUNT) cnt.samples++;
+        if (c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
+            const float vx = fsub(a.lx, px), vy = fsub(a.ly, py), vz = fsub(a.lz, pz);
+            const float len2 = fadd(fadd(fmul(vx, vx), fmul(vy, vy)), fmul(vz, vz));
+            const float inv = fdiv(1.0f, __fsqrt_rn(len2));
+            const float qx = fadd(px, fmul(fmul(vx, inv), 0.01f));
+            const float qy = fadd(py, fmul(fmul(vy, inv), 0.01f));
+            const float qz = fadd(pz, fmul(fmul(vz, inv), 0.01f));
+            const uint32_t sl = sample_volume<SAMPLER>(a, qx, qy, qz);
+            const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s, 255.0f)), a.kd);
+            c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
+            if (COUNT) cnt.shaded++;
+        }
+        const float t = fsub(1.0f, aa);
+        ar = fadd(ar, fmul(c.x, t)); ag = fadd(ag, fmul(c.y, t)); ab = fadd(ab, fmul(c.z, t)); aa = fadd(aa, fmul(c.w, t));
+        if (aa > a.threshold) break;  // early ray termination, strict >
+        k = fadd(k, a.step);
+        px = fadd(ox, fmul(dx, k)); py = fadd(oy, fmul(dy, k)); pz = fadd(oz, fmul(dz, k));
+    }
+    // Raycaster::write_color (RaycasterBase.h:44-50)
+    return trunc_clamp(fmul(ar, 256.0f), 255u) | (trunc_clamp(fmul(ag, 256.0f), 255u) << 8) |
+           (trunc_clamp(fmul(ab, 256.0f), 255u) << 16) | (trunc_clamp(fmul(aa, 256.0f), 255u) << 24);
+}
+
+// ---- the kernel: persistent warps + atomic tile queue -----------------------------------------------------------------
+template <int SAMPLER, bool COUNT>
+__global__ void __launch_bounds__(kCtaThreads) cast_kernel(const __grid_constant__ KArgs a) {
+    __shared__ float4 s_lut[256];
+    __shared__ uint32_t s_esl[1024];
+    for (int i = threadIdx.x; i < 256; i += kCtaThreads) s_lut[i] = a.tf[i >> 1];
+    for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) *a.queue_next = 0u;  // arm the other counter for the next frame
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    Counters cnt = {0, 0, 0, 0, 0};
+    for (;;) {
+        unsigned q = 0;
+        if (lane == 0) q = atomicAdd(a.queue, 1u);
+        q = __shfl_sync(0xffffffffu, q, 0);
+        if (q >= a.n_queue) break;
+        const uint32_t group = q / (kGroupTilesX * kGroupTilesY), within = q % (kGroupTilesX * kGroupTilesY);
+        const uint32_t tx = (group % a.groups_x) * kGroupTilesX + (within % kGroupTilesX);
+        const uint32_t tyl = (group / a.groups_x) * kGroupTilesY + (within / kGroupTilesX);
+        if (tx >= a.tiles_x || tyl >= a.tile_rows_local) continue;
+        const int col = (int)tx * kTileW + (lane & 7);
+        const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
+        if (col < a.width && row < a.height) {  // ragged right / bottom edge: lanes outside the image idle
+            const uint32_t rgba = cast_ray<SAMPLER, COUNT>(a, s_lut, s_esl, col, row, cnt);
+            if (!COUNT) {
+                const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
+                reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;
+            }
+        }
+    }
+    if (COUNT) {
+        unsigned long long v[5] = {cnt.rays_hit, cnt.rays_accum, cnt.esl_iters, cnt.samples, cnt.shaded};
+        unsigned long long *dst = reinterpret_cast<unsigned long long *>(a.counters);
+#pragma unroll
+        for (int i = 0; i < 5; i++) {
+            unsigned long long x = v[i];
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+            if (lane == 0 && x) atomicAdd(dst + i, x);
+        }
+    }
+}
+
+}  // namespace vr5

@@ -1,0 +1,490 @@
+// vr5_render.cu - host side of the C ABI (include/vr5.h): device state, layouts, launches, timing.
+// Replaces the frame drivers of the reference's CUDA renderers (GPURenderer1.cu:65-112, GPURenderer23.cu:55-81,
+// GPURenderer4.cu:89-153) with one renderer that owns all of its device state.
+#include <cuda_runtime.h>
+
+#include <limits>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "../../include/vr5.h"
+#include "vr5_cast.cuh"
+#include "vr5_internal.h"
+
+using namespace vr5;
+
+static std::string g_create_error;
+
+void vr5_fail(vr5_renderer *r, const char *what, cudaError_t e, const char *file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof(buf), "%s: %s (%s:%d)", what, e == cudaSuccess ? "invalid argument" : cudaGetErrorString(e), file, line);
+    if (r) r->err = buf; else g_create_error = buf;
+}
+
+// ---- layout kernels --------------------------------------------------------------------------------------------
+// linear (x fastest) -> 8x4x4 bricks, one thread per 4 consecutive x voxels of the padded brick grid
+__global__ void brick_layout_kernel(const uint8_t *__restrict__ lin, uint8_t *__restrict__ brick, uint32_t nx, uint32_t ny,
+                                    uint32_t nz, uint32_t bxn, uint32_t byn, uint32_t bzn) {
+    const uint64_t n_words = (uint64_t)bxn * byn * bzn * 32u;  // 32 x 4-byte words per brick
+    for (uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t b = w >> 5;
+        const uint32_t in = (uint32_t)(w & 31u) << 2;  // byte offset of the word inside the brick, bits: x0 x1 y0 y1 z0 x2 z1
+        const uint32_t lx = ((in >> 5) & 1u) << 2, ly = (in >> 2) & 3u, lz = ((in >> 4) & 1u) | (((in >> 6) & 1u) << 1);
+        const uint32_t bx = (uint32_t)(b % bxn), by = (uint32_t)((b / bxn) % byn), bz = (uint32_t)(b / ((uint64_t)bxn * byn));
+        const uint32_t x = bx * 8u + lx, y = by * 4u + ly, z = bz * 4u + lz;
+        uint32_t v = 0;
+        if (y < ny && z < nz) {
+            const uint8_t *src = lin + ((uint64_t)z * ny + y) * nx + x;
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (x + i < nx) v |= (uint32_t)src[i] << (8 * i);
+        }
+        reinterpret_cast<uint32_t *>(brick)[w] = v;
+    }
+}
+
+__global__ void unpack_strips_kernel(const uint32_t *__restrict__ packed, uint32_t rows_padded, int world, uint32_t width,
+                                     uint32_t height, uint32_t *__restrict__ frame) {
+    const uint64_t n = (uint64_t)width * height;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t row = (uint32_t)(i / width), col = (uint32_t)(i % width);
+        const uint32_t strip = row / kTileH, rank = strip % world, local = strip / world;
+        frame[i] = packed[((uint64_t)rank * rows_padded + local * kTileH + row % kTileH) * width + col];
+    }
+}
+
+__global__ void l2_flush_kernel(uint32_t *buf, uint64_t n_words, uint32_t v) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (uint64_t)gridDim.x * blockDim.x) buf[i] = v;
+}
+
+// ---- lifecycle ---------------------------------------------------------------------------------------------------
+extern "C" int vr5_version(void) { return VR5_VERSION; }
+extern "C" const char *vr5_name(void) { return "CUDA B200 persistent tile queue (GPURenderer5)"; }
+extern "C" const char *vr5_last_error(const vr5_renderer *r) { return r ? r->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int vr5_create(int device, vr5_renderer **out) {
+    if (!out) return 1;
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        vr5_fail(nullptr, "vr5_create: no CUDA device (there is no CPU fallback)", e, __FILE__, __LINE__);
+        return 1;
+    }
+    if (device < 0) { e = cudaGetDevice(&device); if (e != cudaSuccess) { vr5_fail(nullptr, "cudaGetDevice", e, __FILE__, __LINE__); return 1; } }
+    if (device >= n_dev) { vr5_fail(nullptr, "vr5_create: device ordinal out of range", cudaSuccess, __FILE__, __LINE__); return 1; }
+    vr5_renderer *r = new vr5_renderer();
+    r->device = device;
+    auto bail = [&](const char *what, cudaError_t err) { vr5_fail(nullptr, what, err, __FILE__, __LINE__); vr5_destroy(r); return 1; };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
+    r->num_sms = prop.multiProcessorCount;
+    r->l2_bytes = (size_t)prop.l2CacheSize;
+    if ((e = cudaStreamCreateWithFlags(&r->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    r->stream = r->own_stream;
+    if ((e = cudaMalloc(&r->d_tf, VR5_TF_SIZE * sizeof(float4))) != cudaSuccess) return bail("cudaMalloc tf", e);
+    if ((e = cudaMalloc(&r->d_esl, VR5_ESL_VOLUME_SIZE * sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc esl", e);
+    if ((e = cudaMalloc(&r->d_queue, 2 * sizeof(unsigned))) != cudaSuccess) return bail("cudaMalloc queue", e);
+    if ((e = cudaMemset(r->d_queue, 0, 2 * sizeof(unsigned))) != cudaSuccess) return bail("cudaMemset queue", e);
+    if ((e = cudaMalloc(&r->d_counters, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc counters", e);
+    const char *env = getenv("VR5_SAMPLER");
+    r->sampler = VR5_SAMPLER_LINEAR;
+    if (env) {
+        if (!strcmp(env, "brick") || !strcmp(env, "1")) r->sampler = VR5_SAMPLER_BRICK;
+        else if (!strcmp(env, "tex3d") || !strcmp(env, "2")) r->sampler = VR5_SAMPLER_TEX3D;
+    }
+    *out = r;
+    return 0;
+}
+
+static void free_layouts(vr5_renderer *r) {
+    if (r->tex) { cudaDestroyTextureObject(r->tex); r->tex = 0; }
+    if (r->d_array) { cudaFreeArray(r->d_array); r->d_array = nullptr; }
+    if (r->d_vol_brick) { cudaFree(r->d_vol_brick); r->d_vol_brick = nullptr; }
+}
+
+extern "C" void vr5_destroy(vr5_renderer *r) {
+    if (!r) return;
+    cudaSetDevice(r->device);
+    if (r->own_stream) cudaStreamSynchronize(r->own_stream);
+    free_layouts(r);
+    cudaFree(r->d_vol_linear);
+    cudaFree(r->d_frame);
+    cudaFree(r->d_tf);
+    cudaFree(r->d_esl);
+    cudaFree(r->d_queue);
+    cudaFree(r->d_counters);
+    cudaFree(r->d_flush);
+    if (r->own_stream) cudaStreamDestroy(r->own_stream);
+    delete r;
+}
+
+// ---- scene state -------------------------------------------------------------------------------------------------
+extern "C" int vr5_set_window(vr5_renderer *r, uint16_t width, uint16_t height) {
+    if (!r) return 1;
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    if (width == 0 || height == 0) { vr5_fail(r, "vr5_set_window: empty viewport", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    if (r->d_frame) { cudaFree(r->d_frame); r->d_frame = nullptr; }
+    r->width = width; r->height = height;
+    r->frame_bytes = (size_t)width * height * 4;
+    VR5_CUDA(r, cudaMalloc(&r->d_frame, r->frame_bytes));
+    return 0;
+}
+
+extern "C" int vr5_set_transfer_fn(vr5_renderer *r, const float *tf, const uint32_t *esl_bits) {
+    if (!r) return 1;
+    if (!tf || !esl_bits) { vr5_fail(r, "vr5_set_transfer_fn: NULL table", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaMemcpyAsync(r->d_tf, tf, VR5_TF_SIZE * sizeof(float4), cudaMemcpyHostToDevice, r->stream));
+    VR5_CUDA(r, cudaMemcpyAsync(r->d_esl, esl_bits, VR5_ESL_VOLUME_SIZE * sizeof(uint32_t), cudaMemcpyHostToDevice, r->stream));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    r->have_tf = true;
+    return 0;
+}
+
+static int build_layout(vr5_renderer *r) {
+    free_layouts(r);
+    if (!r->d_vol_linear) return 0;
+    if (r->sampler == VR5_SAMPLER_BRICK) {
+        r->bxn = (r->nx + 7u) / 8u; r->byn = (r->ny + 3u) / 4u; r->bzn = (r->nz + 3u) / 4u;
+        const uint64_t bytes = (uint64_t)r->bxn * r->byn * r->bzn * 128u;
+        cudaError_t e = cudaMalloc(&r->d_vol_brick, bytes);
+        if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc bricked volume", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
+        brick_layout_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, r->d_vol_brick, r->nx, r->ny, r->nz, r->bxn, r->byn, r->bzn);
+        r->launches++;
+        VR5_CUDA(r, cudaGetLastError());
+        VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    } else if (r->sampler == VR5_SAMPLER_TEX3D) {
+        cudaChannelFormatDesc desc = cudaCreateChannelDesc(8, 0, 0, 0, cudaChannelFormatKindUnsigned);
+        cudaExtent ext = make_cudaExtent(r->nx, r->ny, r->nz);
+        cudaError_t e = cudaMalloc3DArray(&r->d_array, &desc, ext, 0);
+        if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc3DArray", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
+        cudaMemcpy3DParms cp;
+        memset(&cp, 0, sizeof(cp));
+        cp.srcPtr = make_cudaPitchedPtr(r->d_vol_linear, r->nx, r->nx, r->ny);
+        cp.dstArray = r->d_array;
+        cp.extent = ext;
+        cp.kind = cudaMemcpyDeviceToDevice;
+        VR5_CUDA(r, cudaMemcpy3DAsync(&cp, r->stream));
+        VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+        cudaResourceDesc res;
+        memset(&res, 0, sizeof(res));
+        res.resType = cudaResourceTypeArray;
+        res.res.array.array = r->d_array;
+        cudaTextureDesc td;
+        memset(&td, 0, sizeof(td));
+        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint;
+        td.readMode = cudaReadModeElementType;
+        td.normalizedCoords = 0;
+        VR5_CUDA(r, cudaCreateTextureObject(&r->tex, &res, &td, nullptr));
+    }
+    return 0;
+}
+
+static int install_volume(vr5_renderer *r, const uint8_t *src, cudaMemcpyKind kind, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz) {
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    free_layouts(r);
+    if (r->d_vol_linear) { cudaFree(r->d_vol_linear); r->d_vol_linear = nullptr; }
+    r->vol_bytes = 0;
+    if (!src) { vr5_fail(r, "vr5_set_volume: no data", cudaSuccess, __FILE__, __LINE__); return 1; }  // GPURenderer1.cu:91-92
+    if (dx == 0 || dy == 0 || dz == 0 || bytes != (uint64_t)dx * dy * dz) {
+        vr5_fail(r, "vr5_set_volume: bytes != dx*dy*dz", cudaSuccess, __FILE__, __LINE__);
+        return 1;
+    }
+    cudaError_t e = cudaMalloc(&r->d_vol_linear, bytes);
+    if (e != cudaSuccess) {  // GPURenderer1.cu:93-95: allocation failure is a soft error
+        vr5_fail(r, "cudaMalloc volume (data is probably too large for device memory)", e, __FILE__, __LINE__);
+        cudaGetLastError();
+        r->d_vol_linear = nullptr;
+        return 1;
+    }
+    if (src != r->d_vol_linear) VR5_CUDA(r, cudaMemcpyAsync(r->d_vol_linear, src, bytes, kind, r->stream));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    r->vol_bytes = bytes; r->nx = dx; r->ny = dy; r->nz = dz;
+    return build_layout(r);
+}
+
+extern "C" int vr5_set_volume(vr5_renderer *r, const uint8_t *host, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz) {
+    if (!r) return 1;
+    return install_volume(r, host, cudaMemcpyHostToDevice, bytes, dx, dy, dz);
+}
+
+extern "C" int vr5_set_volume_device(vr5_renderer *r, const uint8_t *dev, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz) {
+    if (!r) return 1;
+    return install_volume(r, dev, cudaMemcpyDeviceToDevice, bytes, dx, dy, dz);
+}
+
+// adopt a linear device buffer allocated by this library (device generator) without copying
+int vr5_adopt_volume(vr5_renderer *r, uint8_t *dev_owned, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz) {
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    free_layouts(r);
+    if (r->d_vol_linear) cudaFree(r->d_vol_linear);
+    r->d_vol_linear = dev_owned; r->vol_bytes = bytes; r->nx = dx; r->ny = dy; r->nz = dz;
+    return build_layout(r);
+}
+
+extern "C" int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes) {
+    if (!r) return 1;
+    if (!r->d_vol_linear || !host_out || bytes != r->vol_bytes) { vr5_fail(r, "vr5_get_volume: no volume / size mismatch", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaMemcpyAsync(host_out, r->d_vol_linear, bytes, cudaMemcpyDeviceToHost, r->stream));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    return 0;
+}
+
+extern "C" int vr5_set_sampler(vr5_renderer *r, int sampler) {
+    if (!r) return 1;
+    if (sampler < 0 || sampler > 2) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    if (sampler == r->sampler && (sampler == VR5_SAMPLER_LINEAR || r->d_vol_brick || r->tex)) return 0;
+    r->sampler = sampler;
+    return build_layout(r);
+}
+extern "C" int vr5_get_sampler(const vr5_renderer *r) { return r ? r->sampler : -1; }
+
+extern "C" int vr5_set_partition(vr5_renderer *r, int rank, int world, int packed) {
+    if (!r) return 1;
+    if (world < 1 || rank < 0 || rank >= world) { vr5_fail(r, "vr5_set_partition: need 0 <= rank < world", cudaSuccess, __FILE__, __LINE__); return 1; }
+    r->rank = rank; r->world = world; r->packed = packed ? 1 : 0;
+    return 0;
+}
+
+extern "C" uint32_t vr5_strip_rows(uint16_t height, int rank, int world) {
+    if (world < 1 || rank < 0 || rank >= world) return 0;
+    const uint32_t strips = (height + kTileH - 1) / kTileH;
+    if ((uint32_t)rank >= strips) return 0;
+    const uint32_t owned = (strips - rank + world - 1) / world;
+    const uint32_t last_strip = rank + (owned - 1) * world;
+    const uint32_t last_rows = (last_strip == strips - 1 && height % kTileH) ? height % kTileH : kTileH;
+    return (owned - 1) * kTileH + last_rows;
+}
+
+// ---- launch ------------------------------------------------------------------------------------------------------
+template <int S, bool C>
+static cudaError_t launch_one(vr5_renderer *r, const KArgs &a) {
+    int per_sm = r->ctas_per_sm[S][C ? 1 : 0];
+    if (per_sm == 0) {
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cast_kernel<S, C>, kCtaThreads, 0);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) per_sm = 1;
+        r->ctas_per_sm[S][C ? 1 : 0] = per_sm;
+    }
+    uint32_t grid = (uint32_t)(r->num_sms * per_sm);  // persistent: every CTA resident, a multiple of the SM count
+    const uint32_t needed = (a.n_queue + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
+    if (grid > needed) grid = needed ? needed : 1;
+    cast_kernel<S, C><<<grid, kCtaThreads, 0, r->stream>>>(a);
+    r->launches++;
+    return cudaGetLastError();
+}
+
+static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs *a) {
+    if (!p) { vr5_fail(r, "vr5_render: NULL params", cudaSuccess, __FILE__, __LINE__); return 1; }
+    // the reference's own guard (GPURenderer1.cu:101-102): volume, TF + ESL table, buffer
+    if (!r->d_vol_linear || !r->have_tf) { vr5_fail(r, "vr5_render: volume or transfer function not set", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (p->view.dims.x != r->width || p->view.dims.y != r->height) { vr5_fail(r, "vr5_render: view dims differ from vr5_set_window", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (p->esl && (p->esl_block_dims == 0 || p->esl_block_dims > 65535u)) { vr5_fail(r, "vr5_render: esl_block_dims must be in 1..65535", cudaSuccess, __FILE__, __LINE__); return 1; }
+    memset(a, 0, sizeof(*a));
+    const vr5_view &v = p->view;
+    a->ox = v.origin.x; a->oy = v.origin.y; a->oz = v.origin.z;
+    a->dx = v.direction.x; a->dy = v.direction.y; a->dz = v.direction.z;
+    a->rx = v.right_plane.x; a->ry = v.right_plane.y; a->rz = v.right_plane.z;
+    a->ux = v.up_plane.x; a->uy = v.up_plane.y; a->uz = v.up_plane.z;
+    a->lx = v.light_pos.x; a->ly = v.light_pos.y; a->lz = v.light_pos.z;
+    a->width = v.dims.x; a->height = v.dims.y;
+    a->half_w = v.dims.x / 2; a->half_h = v.dims.y / 2;
+    a->perspective = v.perspective ? 1 : 0;
+    a->nx1 = r->nx - 1; a->ny1 = r->ny - 1; a->nz1 = r->nz - 1;
+    a->hx = (float)r->nx * 0.5f; a->hy = (float)r->ny * 0.5f; a->hz = (float)r->nz * 0.5f;
+    if (r->sampler == VR5_SAMPLER_BRICK) {
+        a->vol = r->d_vol_brick; a->sx = r->bxn; a->sxy = (uint64_t)r->bxn * r->byn;
+    } else {
+        a->vol = r->d_vol_linear; a->sx = r->nx; a->sxy = (uint64_t)r->nx * r->ny;
+    }
+    a->tex = r->tex;
+    a->mbx = p->min_bound.x; a->mby = p->min_bound.y; a->mbz = p->min_bound.z;
+    a->step = p->ray_step; a->threshold = p->ray_threshold;
+    a->kd = p->light_kd;
+    a->shade_alpha = p->light_kd > 0.01f ? 0.05f : std::numeric_limits<float>::infinity();
+    a->esl = p->esl ? 1 : 0;
+    const uint32_t bd = p->esl_block_dims ? p->esl_block_dims : 1;
+    a->bd_is_one = bd == 1;
+    a->bd_magic = bd == 1 ? 0u : (uint32_t)((0x100000000ull + bd - 1) / bd);
+    a->bsx = p->esl_block_size.x; a->bsy = p->esl_block_size.y; a->bsz = p->esl_block_size.z;
+    a->tf = reinterpret_cast<const float4 *>(r->d_tf);
+    a->esl_bits = r->d_esl;
+    a->out = reinterpret_cast<uchar4 *>(out_dev);
+    a->packed = r->packed; a->rank = r->rank; a->world = r->world;
+    a->tiles_x = (a->width + kTileW - 1) / kTileW;
+    const uint32_t strips = (a->height + kTileH - 1) / kTileH;
+    a->tile_rows_local = (uint32_t)r->rank < strips ? (strips - r->rank + r->world - 1) / r->world : 0;
+    a->groups_x = (a->tiles_x + kGroupTilesX - 1) / kGroupTilesX;
+    const uint32_t groups_y = (a->tile_rows_local + kGroupTilesY - 1) / kGroupTilesY;
+    a->n_queue = a->groups_x * groups_y * (kGroupTilesX * kGroupTilesY);
+    a->queue = r->d_queue + r->parity;
+    a->queue_next = r->d_queue + (r->parity ^ 1);
+    a->counters = reinterpret_cast<Counters *>(r->d_counters);
+    return 0;
+}
+
+static int launch(vr5_renderer *r, const KArgs &a, bool count) {
+    cudaError_t e;
+    switch (r->sampler * 2 + (count ? 1 : 0)) {
+        case 0: e = launch_one<0, false>(r, a); break;
+        case 1: e = launch_one<0, true>(r, a); break;
+        case 2: e = launch_one<1, false>(r, a); break;
+        case 3: e = launch_one<1, true>(r, a); break;
+        case 4: e = launch_one<2, false>(r, a); break;
+        default: e = launch_one<2, true>(r, a); break;
+    }
+    r->parity ^= 1;
+    if (e != cudaSuccess) { vr5_fail(r, "cast_kernel launch", e, __FILE__, __LINE__); return 1; }
+    return 0;
+}
+
+static int resolve_is_device(vr5_renderer *r, const void *ptr, int hint) {
+    if (hint == 0 || hint == 1) return hint;
+    cudaPointerAttributes attr;
+    cudaError_t e = cudaPointerGetAttributes(&attr, ptr);
+    if (e != cudaSuccess) { cudaGetLastError(); return 0; }
+    (void)r;
+    return (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged) ? 1 : 0;
+}
+
+static int render_impl(vr5_renderer *r, const vr5_params *p, void *out, int out_is_device, bool blocking) {
+    if (!r) return 1;
+    if (!out) { vr5_fail(r, "vr5_render: NULL buffer", cudaSuccess, __FILE__, __LINE__); return 1; }  // GPURenderer1.cu:101
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    const int is_dev = resolve_is_device(r, out, out_is_device);
+    if (!is_dev && !r->d_frame) { vr5_fail(r, "vr5_render: vr5_set_window not called", cudaSuccess, __FILE__, __LINE__); return 1; }
+    KArgs a;
+    if (fill_args(r, p, is_dev ? out : (void *)r->d_frame, &a)) return 1;
+    if (launch(r, a, false)) return 1;
+    if (!is_dev) {
+        const size_t rows = r->packed ? vr5_strip_rows(r->height, r->rank, r->world) : r->height;
+        VR5_CUDA(r, cudaMemcpyAsync(out, r->d_frame, rows * r->width * 4, cudaMemcpyDeviceToHost, r->stream));
+    }
+    if (blocking) VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    return 0;
+}
+
+extern "C" int vr5_render(vr5_renderer *r, const vr5_params *p, void *out, int out_is_device) { return render_impl(r, p, out, out_is_device, true); }
+extern "C" int vr5_render_async(vr5_renderer *r, const vr5_params *p, void *out, int out_is_device) { return render_impl(r, p, out, out_is_device, false); }
+
+extern "C" int vr5_render_raycaster(vr5_renderer *r, const vr5_raycaster *rc, void *out, int out_is_device) {
+    if (!r) return 1;
+    if (!rc) { vr5_fail(r, "vr5_render_raycaster: NULL raycaster", cudaSuccess, __FILE__, __LINE__); return 1; }
+    vr5_params p;
+    memset(&p, 0, sizeof(p));
+    p.view = rc->view;
+    p.ray_step = rc->ray_step; p.ray_threshold = rc->ray_threshold;
+    p.esl = rc->esl ? 1 : 0; p.esl_block_dims = rc->esl_block_dims; p.esl_block_size = rc->esl_block_size;
+    p.light_kd = rc->light_kd; p.min_bound = rc->volume.min_bound;
+    return render_impl(r, &p, out, out_is_device, true);
+}
+
+extern "C" int vr5_sync(vr5_renderer *r) {
+    if (!r) return 1;
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    return 0;
+}
+
+extern "C" int vr5_set_stream(vr5_renderer *r, void *cuda_stream) {
+    if (!r) return 1;
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    if (cuda_stream) { r->stream = (cudaStream_t)cuda_stream; r->external_stream = true; }
+    else { r->stream = r->own_stream; r->external_stream = false; }
+    return 0;
+}
+
+// ---- measurement ---------------------------------------------------------------------------------------------------
+extern "C" int vr5_render_timed(vr5_renderer *r, const vr5_params *frames, int n_frames, void *out_dev, int l2_flush, float *ms_out) {
+    if (!r) return 1;
+    if (!frames || n_frames <= 0 || !out_dev || !ms_out) { vr5_fail(r, "vr5_render_timed: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    if (l2_flush && !r->d_flush) {
+        r->flush_bytes = r->l2_bytes * 2 > (256u << 20) ? r->l2_bytes * 2 : (256u << 20);
+        VR5_CUDA(r, cudaMalloc(&r->d_flush, r->flush_bytes));
+    }
+    std::vector<cudaEvent_t> ev(2 * (size_t)n_frames);
+    for (auto &e : ev) VR5_CUDA(r, cudaEventCreate(&e));
+    int rc = 0;
+    for (int f = 0; f < n_frames && !rc; f++) {
+        if (l2_flush) {
+            l2_flush_kernel<<<r->num_sms * 4, 512, 0, r->stream>>>(reinterpret_cast<uint32_t *>(r->d_flush), r->flush_bytes / 4, (uint32_t)f);
+            r->launches++;
+        }
+        KArgs a;
+        if (fill_args(r, frames + f, out_dev, &a)) { rc = 1; break; }
+        cudaEventRecord(ev[2 * f], r->stream);
+        rc = launch(r, a, false);
+        cudaEventRecord(ev[2 * f + 1], r->stream);
+    }
+    cudaError_t e = cudaStreamSynchronize(r->stream);
+    if (e != cudaSuccess) { vr5_fail(r, "vr5_render_timed sync", e, __FILE__, __LINE__); rc = 1; }
+    if (!rc)
+        for (int f = 0; f < n_frames; f++) cudaEventElapsedTime(ms_out + f, ev[2 * f], ev[2 * f + 1]);
+    for (auto &x : ev) cudaEventDestroy(x);
+    return rc;
+}
+
+extern "C" int vr5_count(vr5_renderer *r, const vr5_params *p, vr5_counters *out) {
+    if (!r) return 1;
+    if (!out) { vr5_fail(r, "vr5_count: NULL out", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    KArgs a;
+    if (fill_args(r, p, nullptr, &a)) return 1;
+    VR5_CUDA(r, cudaMemsetAsync(r->d_counters, 0, sizeof(Counters), r->stream));
+    if (launch(r, a, true)) return 1;
+    static_assert(sizeof(Counters) == sizeof(vr5_counters), "counter layout");
+    VR5_CUDA(r, cudaMemcpyAsync(out, r->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, r->stream));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    return 0;
+}
+
+extern "C" uint64_t vr5_launch_count(const vr5_renderer *r) { return r ? r->launches : 0; }
+
+extern "C" void *vr5_host_alloc(uint64_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void vr5_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+extern "C" void *vr5_device_alloc(vr5_renderer *r, uint64_t bytes) {
+    if (!r) return nullptr;
+    void *p = nullptr;
+    if (cudaSetDevice(r->device) != cudaSuccess) return nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) { vr5_fail(r, "vr5_device_alloc", e, __FILE__, __LINE__); cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void vr5_device_free(vr5_renderer *r, void *p) { if (r && p) { cudaSetDevice(r->device); cudaFree(p); } }
+
+extern "C" int vr5_memcpy_d2h(vr5_renderer *r, void *host_dst, const void *dev_src, uint64_t bytes) {
+    if (!r) return 1;
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, r->stream));
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    return 0;
+}
+
+extern "C" int vr5_unpack_strips(vr5_renderer *r, const void *packed_all, uint32_t rows_padded, int world, void *frame) {
+    if (!r) return 1;
+    if (!packed_all || !frame || world < 1 || !r->width) { vr5_fail(r, "vr5_unpack_strips: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    unpack_strips_kernel<<<r->num_sms * 4, 256, 0, r->stream>>>(reinterpret_cast<const uint32_t *>(packed_all), rows_padded, world, r->width, r->height,
+                                                               reinterpret_cast<uint32_t *>(frame));
+    r->launches++;
+    VR5_CUDA(r, cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,228 @@
+"""Python mirror of the reference's Renderer interface over the vr5 C ABI, plus the scene-builder wrappers.
+
+``GPURenderer5`` keeps the reference's method names and return conventions (Renderer.h:13-28; 0 = ok, 1 = failure
+for set_volume / render_volume) so the parity tests read like calls on a VolR renderer. Everything here is a thin
+ctypes call into libvr5.so; no arithmetic of the hot path lives in Python.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import (Counters, F3, Params, SAMPLERS, View, Vr5Error, _f32p, _u32p, _u8p, lib)
+
+
+class Scene:
+    """Host-side bundle of what RaycasterBase::raycaster holds: volume, pre-multiplied TF, ESL bits, march params."""
+
+    def __init__(self, volume, tf_premult, esl_bits, esl_block_dims, esl_block_size, ray_step, ray_threshold=0.95,
+                 esl=True, light_kd=0.6):
+        self.volume = volume  # numpy [dz, dy, dx] uint8, or None when the volume lives on the device only
+        self.tf = np.ascontiguousarray(tf_premult, dtype=np.float32).reshape(128, 4)
+        self.esl_bits = np.ascontiguousarray(esl_bits, dtype=np.uint32).reshape(1024)
+        self.esl_block_dims = int(esl_block_dims)
+        self.esl_block_size = tuple(float(v) for v in esl_block_size)
+        self.ray_step = float(ray_step)
+        self.ray_threshold = float(ray_threshold)
+        self.esl = bool(esl)
+        self.light_kd = float(light_kd)
+
+    def params(self, view: View) -> Params:
+        p = Params()
+        p.view = View.from_buffer_copy(bytes(view))
+        p.ray_step, p.ray_threshold = self.ray_step, self.ray_threshold
+        p.esl, p.esl_block_dims = (1 if self.esl else 0), self.esl_block_dims
+        p.esl_block_size = F3(*self.esl_block_size)
+        p.light_kd = self.light_kd
+        p.min_bound = F3(-1.0, -1.0, -1.0)
+        return p
+
+
+# ---- scene builders (vr5_scene.cpp; RaycasterBase / ViewBase equivalents) ------------------------------------------
+def default_base_tf() -> np.ndarray:
+    t = np.zeros((128, 4), dtype=np.float32)
+    lib().vr5_scene_default_base_tf(_f32p(t))
+    return t
+
+
+def premultiply_tf(base) -> np.ndarray:
+    base = np.ascontiguousarray(base, dtype=np.float32)
+    out = np.zeros((128, 4), dtype=np.float32)
+    lib().vr5_scene_premultiply_tf(_f32p(base), _f32p(out))
+    return out
+
+
+def build_minmax(volume: np.ndarray):
+    dz, dy, dx = volume.shape
+    bd, bs = C.c_uint16(), F3()
+    mm = np.zeros((32768, 2), dtype=np.uint8)
+    lib().vr5_scene_build_minmax(_u8p(volume), dx, dy, dz, C.byref(bd), _u8p(mm), C.byref(bs))
+    return int(bd.value), mm, (bs.x, bs.y, bs.z)
+
+
+def build_esl_bits(tf_premult, minmax) -> np.ndarray:
+    bits = np.zeros(1024, dtype=np.uint32)
+    tf_premult = np.ascontiguousarray(tf_premult, dtype=np.float32)
+    lib().vr5_scene_build_esl_bits(_f32p(tf_premult), _u8p(minmax), _u32p(bits))
+    return bits
+
+
+def default_ray_step(dx, dy, dz) -> float:
+    return float(lib().vr5_scene_default_ray_step(dx, dy, dz))
+
+
+def camera(width, height, perspective, angles, distance=2.0) -> View:
+    v = View()
+    lib().vr5_scene_camera(width, height, 1 if perspective else 0, angles[0], angles[1], angles[2], distance, C.byref(v))
+    return v
+
+
+def tf_semi(n: int) -> np.ndarray:
+    """SURVEY 8(d) `semi`: default colours, alpha == 1/N everywhere (no early termination, no shading)."""
+    t = default_base_tf()
+    t[:, 3] = np.float32(1.0) / np.float32(n)
+    return t
+
+
+def tf_opaque() -> np.ndarray:
+    """SURVEY 8(d) `opaque`: alpha 1 for TF index >= 64, else 0."""
+    t = default_base_tf()
+    t[:, 3] = 0.0
+    t[64:, 3] = 1.0
+    return t
+
+
+class GPURenderer5:
+    """``class GPURenderer5 : public Renderer`` as seen from Python (same calls as GPURenderer1.cu:17-112)."""
+
+    def __init__(self, device: int = -1, sampler: str | int | None = None):
+        self._L = lib()
+        h = C.c_void_p()
+        if self._L.vr5_create(device, C.byref(h)) != 0:
+            raise Vr5Error(self._L.vr5_last_error(None).decode())
+        self._h = h
+        self._keep = []
+        if sampler is not None:
+            self.set_sampler(sampler)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.vr5_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _check(self, rc, soft=False):
+        if rc != 0 and not soft:
+            raise Vr5Error(self.last_error())
+        return rc
+
+    def last_error(self) -> str:
+        return self._L.vr5_last_error(self._h).decode()
+
+    def get_name(self) -> str:
+        return self._L.vr5_name().decode()
+
+    # -- Renderer interface -----------------------------------------------------------------------------------------
+    def set_window_buffer(self, width: int, height: int):
+        self._check(self._L.vr5_set_window(self._h, width, height))
+        self.width, self.height = width, height
+
+    def set_transfer_fn(self, tf_premult, esl_bits):
+        tf = np.ascontiguousarray(tf_premult, dtype=np.float32)
+        bits = np.ascontiguousarray(esl_bits, dtype=np.uint32)
+        self._check(self._L.vr5_set_transfer_fn(self._h, _f32p(tf), _u32p(bits)))
+
+    def set_volume(self, volume) -> int:
+        """0 ok / 1 failure like the reference (GPURenderer1.cu:86-98); ``None`` = no data."""
+        if volume is None:
+            return self._L.vr5_set_volume(self._h, None, 0, 0, 0, 0)
+        volume = np.ascontiguousarray(volume, dtype=np.uint8)
+        dz, dy, dx = volume.shape
+        return self._L.vr5_set_volume(self._h, _u8p(volume), volume.size, dx, dy, dz)
+
+    def render_volume(self, params: Params, out: np.ndarray | None = None) -> np.ndarray:
+        """Blocking render into a host array [H, W, 4] uint8 (host-pointer path of render_volume)."""
+        w, h = params.view.dims[0], params.view.dims[1]
+        if out is None:
+            out = np.empty((h, w, 4), dtype=np.uint8)
+        self._check(self._L.vr5_render(self._h, C.byref(params), out.ctypes.data, 0))
+        return out
+
+    def render_raycaster(self, rc_bytes_ptr, out: np.ndarray) -> int:
+        return self._L.vr5_render_raycaster(self._h, rc_bytes_ptr, out.ctypes.data, 0)
+
+    # -- extras -----------------------------------------------------------------------------------------------------
+    def set_scene(self, scene: Scene):
+        if scene.volume is not None:
+            self._check(self.set_volume(scene.volume))
+        self.set_transfer_fn(scene.tf, scene.esl_bits)
+
+    def set_sampler(self, sampler):
+        s = SAMPLERS[sampler] if isinstance(sampler, str) else int(sampler)
+        self._check(self._L.vr5_set_sampler(self._h, s))
+
+    def synth_volume(self, kind: int, n: int, seed: int):
+        self._check(self._L.vr5_synth_volume(self._h, kind, n, seed))
+
+    def get_volume(self, shape) -> np.ndarray:
+        out = np.empty(shape, dtype=np.uint8)
+        self._check(self._L.vr5_get_volume(self._h, _u8p(out), out.size))
+        return out
+
+    def count(self, params: Params) -> dict:
+        c = Counters()
+        self._check(self._L.vr5_count(self._h, C.byref(params), C.byref(c)))
+        return c.as_dict()
+
+    def render_device(self, params: Params, dev_ptr: int, blocking=True):
+        fn = self._L.vr5_render if blocking else self._L.vr5_render_async
+        self._check(fn(self._h, C.byref(params), dev_ptr, 1))
+
+    def render_to_pinned(self, params: Params, host_ptr: int):
+        self._check(self._L.vr5_render(self._h, C.byref(params), host_ptr, 0))
+
+    def render_timed(self, frames, dev_ptr: int, l2_flush=False) -> np.ndarray:
+        arr = (Params * len(frames))(*frames)
+        ms = np.zeros(len(frames), dtype=np.float32)
+        self._check(self._L.vr5_render_timed(self._h, arr, len(frames), dev_ptr, 1 if l2_flush else 0, _f32p(ms)))
+        return ms
+
+    def sync(self):
+        self._check(self._L.vr5_sync(self._h))
+
+    def set_stream(self, stream_ptr):
+        self._check(self._L.vr5_set_stream(self._h, stream_ptr))
+
+    def set_partition(self, rank, world, packed):
+        self._check(self._L.vr5_set_partition(self._h, rank, world, 1 if packed else 0))
+
+    def unpack_strips(self, packed_ptr, rows_padded, world, frame_ptr):
+        self._check(self._L.vr5_unpack_strips(self._h, packed_ptr, rows_padded, world, frame_ptr))
+
+    def device_alloc(self, nbytes) -> int:
+        p = self._L.vr5_device_alloc(self._h, nbytes)
+        if not p:
+            raise Vr5Error(self.last_error())
+        return p
+
+    def device_free(self, p):
+        self._L.vr5_device_free(self._h, p)
+
+    def memcpy_d2h(self, host: np.ndarray, dev_ptr: int):
+        self._check(self._L.vr5_memcpy_d2h(self._h, host.ctypes.data, dev_ptr, host.nbytes))
+
+    def launch_count(self) -> int:
+        return int(self._L.vr5_launch_count(self._h))
+
+    def build_minmax_device(self):
+        bd, bs = C.c_uint16(), F3()
+        mm = np.zeros((32768, 2), dtype=np.uint8)
+        self._check(self._L.vr5_build_minmax_device(self._h, C.byref(bd), _u8p(mm), C.byref(bs)))
+        return int(bd.value), mm, (bs.x, bs.y, bs.z)
+
+    def histogram_device(self) -> np.ndarray:
+        h = np.zeros(256, dtype=np.float32)
+        self._check(self._L.vr5_histogram_device(self._h, _f32p(h)))
+        return h
