@@ -109,12 +109,34 @@ __device__ __forceinline__ uint32_t fetch_voxel<2>(const KArgs &a, uint32_t ix, 
     return r0;
 }
 
-template <int SAMPLER>
-__device__ __forceinline__ uint32_t sample_volume(const KArgs &a, float px, float py, float pz) {
-    uint32_t iz = world_to_voxel(pz, a.hz, a.nz1);
-    uint32_t iy = world_to_voxel(py, a.hy, a.ny1);
-    uint32_t ix = world_to_voxel(px, a.hx, a.nx1);
+// Voxel index triple of a world-space point. CLAMP=false drops the upper clamp: legal only for the 3-D texture, which is
+// padded by one replicated voxel per axis (index n == index n-1) and cannot fault; rays clipped to [-1,1]^3 never reach
+// index n+1 (p <= 1 + a few ulp). The lower clamp is the saturation of cvt.rzi.u32.f32 either way.
+struct VolScale { float hx, hy, hz; };  // dims * 0.5f held in registers
+
+template <int SAMPLER, bool CLAMP>
+__device__ __forceinline__ uint32_t sample_volume(const KArgs &a, const VolScale &v, float px, float py, float pz) {
+    uint32_t iz, iy, ix;
+    if (CLAMP) {
+        iz = world_to_voxel(pz, v.hz, a.nz1); iy = world_to_voxel(py, v.hy, a.ny1); ix = world_to_voxel(px, v.hx, a.nx1);
+    } else {
+        iz = __float2uint_rz(fmul(fadd(pz, 1.0f), v.hz));
+        iy = __float2uint_rz(fmul(fadd(py, 1.0f), v.hy));
+        ix = __float2uint_rz(fmul(fadd(px, 1.0f), v.hx));
+    }
     return fetch_voxel<SAMPLER>(a, ix, iy, iz);
+}
+
+// Loop-invariant kernel parameters are bounced through shared memory once per CTA and read back with volatile loads:
+// that pins them in general registers for the whole march. Left alone, ptxas re-reads them from the constant bank
+// through the uniform datapath (LDCU) on every iteration - one issue slot each in an issue-bound loop (profiles/).
+struct Pinned { float hx, hy, hz, step, threshold; };
+
+// LUT fetch through a 32-bit shared-window address kept in a register (avoids recomputing the window base per sample)
+__device__ __forceinline__ float4 lut_fetch(uint32_t lut_addr, uint32_t s) {
+    float4 c;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w) : "r"(lut_addr + (s << 4)));
+    return c;
 }
 
 __device__ __forceinline__ uint32_t div_block(const KArgs &a, uint32_t idx) {
@@ -122,9 +144,9 @@ __device__ __forceinline__ uint32_t div_block(const KArgs &a, uint32_t idx) {
 }
 
 // ---- one ray (CPURenderer.cpp:11-41). Returns the packed RGBA8 pixel; 0 when the reference leaves it cleared. ----
-template <int SAMPLER, bool COUNT>
-__device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const float4 *lut, const uint32_t *esl_bits, int col, int row,
-                                             Counters &cnt) {
+template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
+__device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs, uint32_t lut_addr, const uint32_t *esl_bits,
+                                             float step, float threshold, int col, int row, Counters &cnt) {
     // View::get_ray (ViewBase.h:23-35)
     const float cx = (float)(col - a.half_w);
     const float cy = (float)(row - a.half_h);
@@ -159,9 +181,9 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const float4 *lut, 
     // leading empty-space loop (CPURenderer.cpp:18-25; sample_data_esl RaycasterBase.h:52-65; leap RaycasterBase.h:67-85)
     if (a.esl) {
         while (k <= k_far) {
-            uint32_t bx = div_block(a, world_to_voxel(px, a.hx, a.nx1));
-            uint32_t by = div_block(a, world_to_voxel(py, a.hy, a.ny1));
-            uint32_t bz = div_block(a, world_to_voxel(pz, a.hz, a.nz1));
+            uint32_t bx = div_block(a, world_to_voxel(px, vs.hx, a.nx1));
+            uint32_t by = div_block(a, world_to_voxel(py, vs.hy, a.ny1));
+            uint32_t bz = div_block(a, world_to_voxel(pz, vs.hz, a.nz1));
             const uint32_t word = esl_bits[(bz * 32u + by) & 1023u];
             if (((word >> (bx & 31u)) & 1u) == 0u) break;
             if (dx > 0.0f) bx++;
@@ -176,39 +198,45 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const float4 *lut, 
             float dk = sel_min(kx, ky);
             dk = sel_min(dk, kz);
             dk = sel_max(dk, 0.0f);
-            dk = fmul(floorf(fdiv(dk, a.step)), a.step);
+            dk = fmul(floorf(fdiv(dk, step)), step);
             k = fadd(k, dk);
             if (COUNT) cnt.esl_iters++;
-            k = fadd(k, a.step);
+            k = fadd(k, step);
             px = fadd(ox, fmul(dx, k)); py = fadd(oy, fmul(dy, k)); pz = fadd(oz, fmul(dz, k));
         }
         if (k > k_far) return 0u;
     }
     if (COUNT) cnt.rays_accum++;
 
-    // accumulation loop (CPURenderer.cpp:28-39)
+    // accumulation loop (CPURenderer.cpp:28-39), software pipelined: the voxel of sample i+1 is requested before sample i
+    // is classified and composited, so its latency overlaps the LUT fetch and the compositing chain. The prefetch is
+    // speculative (it may lie beyond k_far; clamped index or padded texture make it harmless) and changes no result.
+    if (!(k <= k_far)) return 0u;  // NaN interval: the reference writes an all-zero pixel
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
-    while (k <= k_far) {
-        const uint32_t s = sample_volume<SAMPLER>(a, px, py, pz);
-        float4 c = lut[s];  // lut[s] == transfer_fn[s / TF_RATIO]
+    uint32_t s = sample_volume<SAMPLER, CLAMP>(a, vs, px, py, pz);
+    for (;;) {
+        const float kn = fadd(k, step);
+        const float nx = fadd(ox, fmul(dx, kn)), ny = fadd(oy, fmul(dy, kn)), nz = fadd(oz, fmul(dz, kn));
+        const uint32_t sn = sample_volume<SAMPLER, CLAMP>(a, vs, nx, ny, nz);
+        float4 c = lut_fetch(lut_addr, s);  // lut[s] == transfer_fn[s / TF_RATIO]
         if (COUNT) cnt.samples++;
-        if (c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
+        if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
             const float vx = fsub(a.lx, px), vy = fsub(a.ly, py), vz = fsub(a.lz, pz);
             const float len2 = fadd(fadd(fmul(vx, vx), fmul(vy, vy)), fmul(vz, vz));
             const float inv = fdiv(1.0f, __fsqrt_rn(len2));
             const float qx = fadd(px, fmul(fmul(vx, inv), 0.01f));
             const float qy = fadd(py, fmul(fmul(vy, inv), 0.01f));
             const float qz = fadd(pz, fmul(fmul(vz, inv), 0.01f));
-            const uint32_t sl = sample_volume<SAMPLER>(a, qx, qy, qz);
+            const uint32_t sl = sample_volume<SAMPLER, true>(a, vs, qx, qy, qz);  // may leave the cube: always clamped
             const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s, 255.0f)), a.kd);
             c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
             if (COUNT) cnt.shaded++;
         }
         const float t = fsub(1.0f, aa);
         ar = fadd(ar, fmul(c.x, t)); ag = fadd(ag, fmul(c.y, t)); ab = fadd(ab, fmul(c.z, t)); aa = fadd(aa, fmul(c.w, t));
-        if (aa > a.threshold) break;  // early ray termination, strict >
-        k = fadd(k, a.step);
-        px = fadd(ox, fmul(dx, k)); py = fadd(oy, fmul(dy, k)); pz = fadd(oz, fmul(dz, k));
+        if (aa > threshold) break;   // early ray termination, strict >
+        if (!(kn <= k_far)) break;   // while (k <= k_far)
+        k = kn; px = nx; py = ny; pz = nz; s = sn;
     }
     // Raycaster::write_color (RaycasterBase.h:44-50)
     return trunc_clamp(fmul(ar, 256.0f), 255u) | (trunc_clamp(fmul(ag, 256.0f), 255u) << 8) |
@@ -216,16 +244,24 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const float4 *lut, 
 }
 
 // ---- the kernel: persistent warps + atomic tile queue -----------------------------------------------------------------
-template <int SAMPLER, bool COUNT>
+// SHADE=false is chosen by the host when no sample can take the shading path (light_kd <= 0.01 or no TF entry with
+// alpha > 0.05), CLAMP=false when the sampler is the padded 3-D texture and min_bound == (-1,-1,-1).
+template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
 __global__ void __launch_bounds__(kCtaThreads) cast_kernel(const __grid_constant__ KArgs a) {
     __shared__ float4 s_lut[256];
     __shared__ uint32_t s_esl[1024];
+    __shared__ Pinned s_pinned;
     for (int i = threadIdx.x; i < 256; i += kCtaThreads) s_lut[i] = a.tf[i >> 1];
     for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
     if (blockIdx.x == 0 && threadIdx.x == 0) *a.queue_next = 0u;  // arm the other counter for the next frame
+    if (threadIdx.x == 0) s_pinned = Pinned{a.hx, a.hy, a.hz, a.step, a.threshold};
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
+    const volatile Pinned *pinned = &s_pinned;
+    const VolScale vs = {pinned->hx, pinned->hy, pinned->hz};
+    const float step = pinned->step, threshold = pinned->threshold;
+    const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_lut);
     Counters cnt = {0, 0, 0, 0, 0};
     for (;;) {
         unsigned q = 0;
@@ -239,7 +275,7 @@ __global__ void __launch_bounds__(kCtaThreads) cast_kernel(const __grid_constant
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
         if (col < a.width && row < a.height) {  // ragged right / bottom edge: lanes outside the image idle
-            const uint32_t rgba = cast_ray<SAMPLER, COUNT>(a, s_lut, s_esl, col, row, cnt);
+            const uint32_t rgba = cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, vs, lut_addr, s_esl, step, threshold, col, row, cnt);
             if (!COUNT) {
                 const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
                 reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;

@@ -20,6 +20,7 @@ struct vr5_renderer {
     float *d_tf = nullptr;        // 128 x float4, pre-multiplied
     uint32_t *d_esl = nullptr;    // 1024 words
     bool have_tf = false;
+    bool tf_can_shade = false;    // some TF entry has alpha > 0.05 (CPURenderer.cpp:32)
     // volume
     uint8_t *d_vol_linear = nullptr;  // always kept: source of every layout, of vr5_get_volume and of the min/max builder
     uint64_t vol_bytes = 0;
@@ -36,7 +37,7 @@ struct vr5_renderer {
     // partition
     int rank = 0, world = 1, packed = 0;
     // bookkeeping
-    int ctas_per_sm[3][2] = {{0, 0}, {0, 0}, {0, 0}};
+    int ctas_per_sm[24] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
     void *d_flush = nullptr;
     size_t flush_bytes = 0;

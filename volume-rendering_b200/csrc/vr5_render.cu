@@ -46,6 +46,17 @@ __global__ void brick_layout_kernel(const uint8_t *__restrict__ lin, uint8_t *__
     }
 }
 
+// linear -> linear padded by one replicated voxel at the upper end of every axis (source of the 3-D texture: lets the
+// march drop its upper index clamp, see sample_volume<.., CLAMP=false>)
+__global__ void pad_edge_kernel(const uint8_t *__restrict__ lin, uint8_t *__restrict__ padded, uint32_t nx, uint32_t ny, uint32_t nz) {
+    const uint32_t px = nx + 1, py = ny + 1, pz = nz + 1;
+    const uint64_t n = (uint64_t)px * py * pz;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t x = (uint32_t)(i % px), y = (uint32_t)((i / px) % py), z = (uint32_t)(i / ((uint64_t)px * py));
+        padded[i] = lin[((uint64_t)min(z, nz - 1) * ny + min(y, ny - 1)) * nx + min(x, nx - 1)];
+    }
+}
+
 __global__ void unpack_strips_kernel(const uint32_t *__restrict__ packed, uint32_t rows_padded, int world, uint32_t width,
                                      uint32_t height, uint32_t *__restrict__ frame) {
     const uint64_t n = (uint64_t)width * height;
@@ -144,6 +155,8 @@ extern "C" int vr5_set_transfer_fn(vr5_renderer *r, const float *tf, const uint3
     VR5_CUDA(r, cudaMemcpyAsync(r->d_esl, esl_bits, VR5_ESL_VOLUME_SIZE * sizeof(uint32_t), cudaMemcpyHostToDevice, r->stream));
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     r->have_tf = true;
+    r->tf_can_shade = false;  // CPURenderer.cpp:32: only entries with alpha > 0.05 ever reach Raycaster::shade
+    for (int i = 0; i < VR5_TF_SIZE; i++) r->tf_can_shade |= tf[4 * i + 3] > 0.05f;
     return 0;
 }
 
@@ -161,17 +174,24 @@ static int build_layout(vr5_renderer *r) {
         VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     } else if (r->sampler == VR5_SAMPLER_TEX3D) {
         cudaChannelFormatDesc desc = cudaCreateChannelDesc(8, 0, 0, 0, cudaChannelFormatKindUnsigned);
-        cudaExtent ext = make_cudaExtent(r->nx, r->ny, r->nz);
+        cudaExtent ext = make_cudaExtent(r->nx + 1, r->ny + 1, r->nz + 1);  // one replicated voxel of padding per axis
         cudaError_t e = cudaMalloc3DArray(&r->d_array, &desc, ext, 0);
         if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc3DArray", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
+        uint8_t *d_padded = nullptr;
+        e = cudaMalloc(&d_padded, (uint64_t)(r->nx + 1) * (r->ny + 1) * (r->nz + 1));
+        if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc padded staging volume", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
+        pad_edge_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, d_padded, r->nx, r->ny, r->nz);
+        r->launches++;
         cudaMemcpy3DParms cp;
         memset(&cp, 0, sizeof(cp));
-        cp.srcPtr = make_cudaPitchedPtr(r->d_vol_linear, r->nx, r->nx, r->ny);
+        cp.srcPtr = make_cudaPitchedPtr(d_padded, r->nx + 1, r->nx + 1, r->ny + 1);
         cp.dstArray = r->d_array;
         cp.extent = ext;
         cp.kind = cudaMemcpyDeviceToDevice;
-        VR5_CUDA(r, cudaMemcpy3DAsync(&cp, r->stream));
-        VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+        e = cudaMemcpy3DAsync(&cp, r->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
+        cudaFree(d_padded);
+        if (e != cudaSuccess) { vr5_fail(r, "3-D texture upload", e, __FILE__, __LINE__); return 1; }
         cudaResourceDesc res;
         memset(&res, 0, sizeof(res));
         res.resType = cudaResourceTypeArray;
@@ -268,21 +288,26 @@ extern "C" uint32_t vr5_strip_rows(uint16_t height, int rank, int world) {
 }
 
 // ---- launch ------------------------------------------------------------------------------------------------------
-template <int S, bool C>
+template <int S, bool C, bool SH, bool CL>
 static cudaError_t launch_one(vr5_renderer *r, const KArgs &a) {
-    int per_sm = r->ctas_per_sm[S][C ? 1 : 0];
+    int &per_sm = r->ctas_per_sm[((S * 2 + (C ? 1 : 0)) * 2 + (SH ? 1 : 0)) * 2 + (CL ? 1 : 0)];
     if (per_sm == 0) {
-        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cast_kernel<S, C>, kCtaThreads, 0);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cast_kernel<S, C, SH, CL>, kCtaThreads, 0);
         if (e != cudaSuccess) return e;
         if (per_sm < 1) per_sm = 1;
-        r->ctas_per_sm[S][C ? 1 : 0] = per_sm;
     }
     uint32_t grid = (uint32_t)(r->num_sms * per_sm);  // persistent: every CTA resident, a multiple of the SM count
     const uint32_t needed = (a.n_queue + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
     if (grid > needed) grid = needed ? needed : 1;
-    cast_kernel<S, C><<<grid, kCtaThreads, 0, r->stream>>>(a);
+    cast_kernel<S, C, SH, CL><<<grid, kCtaThreads, 0, r->stream>>>(a);
     r->launches++;
     return cudaGetLastError();
+}
+
+template <int S, bool CL>
+static cudaError_t launch_sc(vr5_renderer *r, const KArgs &a, bool count, bool shade) {
+    if (count) return shade ? launch_one<S, true, true, CL>(r, a) : launch_one<S, true, false, CL>(r, a);
+    return shade ? launch_one<S, false, true, CL>(r, a) : launch_one<S, false, false, CL>(r, a);
 }
 
 static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs *a) {
@@ -335,14 +360,15 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
 }
 
 static int launch(vr5_renderer *r, const KArgs &a, bool count) {
+    // shading can only trigger when light_kd > 0.01 (folded into shade_alpha) and some TF entry has alpha > 0.05
+    const bool shade = r->tf_can_shade && a.shade_alpha < std::numeric_limits<float>::infinity();
+    // the padded texture may be indexed without the upper clamp when rays are clipped to the cube it covers
+    const bool unclamped = r->sampler == VR5_SAMPLER_TEX3D && a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f;
     cudaError_t e;
-    switch (r->sampler * 2 + (count ? 1 : 0)) {
-        case 0: e = launch_one<0, false>(r, a); break;
-        case 1: e = launch_one<0, true>(r, a); break;
-        case 2: e = launch_one<1, false>(r, a); break;
-        case 3: e = launch_one<1, true>(r, a); break;
-        case 4: e = launch_one<2, false>(r, a); break;
-        default: e = launch_one<2, true>(r, a); break;
+    switch (r->sampler) {
+        case VR5_SAMPLER_LINEAR: e = launch_sc<0, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_BRICK: e = launch_sc<1, true>(r, a, count, shade); break;
+        default: e = unclamped ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
     }
     r->parity ^= 1;
     if (e != cudaSuccess) { vr5_fail(r, "cast_kernel launch", e, __FILE__, __LINE__); return 1; }
