@@ -83,7 +83,7 @@ int vr5_set_volume(vr5_renderer *r, const uint8_t *host_data, uint64_t bytes, ui
 int vr5_set_volume_device(vr5_renderer *r, const uint8_t *dev_data, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz);
 /* Copies the linear grid back to the host (tests: hand the oracle the exact bytes the kernel sees). */
 int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes);
-/* Select VR5_SAMPLER_*; re-lays out the current volume if one is set. Default: VR5_SAMPLER_LINEAR or $VR5_SAMPLER. */
+/* Select VR5_SAMPLER_*; re-lays out the current volume if one is set. Default: VR5_SAMPLER_TEX3D (fastest on B200) or $VR5_SAMPLER. */
 int vr5_set_sampler(vr5_renderer *r, int sampler);
 int vr5_get_sampler(const vr5_renderer *r);
 

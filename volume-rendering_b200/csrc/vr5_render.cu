@@ -103,10 +103,10 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     if ((e = cudaMemset(r->d_queue, 0, 2 * sizeof(unsigned))) != cudaSuccess) return bail("cudaMemset queue", e);
     if ((e = cudaMalloc(&r->d_counters, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc counters", e);
     const char *env = getenv("VR5_SAMPLER");
-    r->sampler = VR5_SAMPLER_LINEAR;
+    r->sampler = VR5_SAMPLER_TEX3D;  // fastest path on B200 (profiles/r01_sampler_choice.md); $VR5_SAMPLER overrides
     if (env) {
         if (!strcmp(env, "brick") || !strcmp(env, "1")) r->sampler = VR5_SAMPLER_BRICK;
-        else if (!strcmp(env, "tex3d") || !strcmp(env, "2")) r->sampler = VR5_SAMPLER_TEX3D;
+        else if (!strcmp(env, "linear") || !strcmp(env, "0")) r->sampler = VR5_SAMPLER_LINEAR;
     }
     *out = r;
     return 0;
