@@ -132,6 +132,15 @@ __device__ __forceinline__ uint32_t sample_volume(const KArgs &a, const VolScale
 // through the uniform datapath (LDCU) on every iteration - one issue slot each in an issue-bound loop (profiles/).
 struct Pinned { float hx, hy, hz, step, threshold; };
 
+// Packed fp32 pairs (sm_100 add/mul.rn.f32x2 -> SASS FADD2 / FMUL2): two IEEE round-to-nearest results per issue slot,
+// bit-identical to the scalar ops. ptxas 12.9 contracts a packed mul feeding a packed add into FFMA2 even with
+// -fmad=false (tools/probe notes in DESIGN.md), so a packed product is only ever consumed by SCALAR adds here.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
 // LUT fetch through a 32-bit shared-window address kept in a register (avoids recomputing the window base per sample)
 __device__ __forceinline__ float4 lut_fetch(uint32_t lut_addr, uint32_t s) {
     float4 c;
@@ -213,27 +222,41 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
     // speculative (it may lie beyond k_far; clamped index or padded texture make it harmless) and changes no result.
     if (!(k <= k_far)) return 0u;  // NaN interval: the reference writes an all-zero pixel
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
+    const f32x2 dxy = pack2(dx, dy), hxy = pack2(vs.hx, vs.hy), one2 = pack2(1.0f, 1.0f);
     uint32_t s = sample_volume<SAMPLER, CLAMP>(a, vs, px, py, pz);
     for (;;) {
+        // next point: o + d*kn, then (p + 1) * (n/2) per axis; x,y packed, z scalar; packed products feed scalar adds
         const float kn = fadd(k, step);
-        const float nx = fadd(ox, fmul(dx, kn)), ny = fadd(oy, fmul(dy, kn)), nz = fadd(oz, fmul(dz, kn));
-        const uint32_t sn = sample_volume<SAMPLER, CLAMP>(a, vs, nx, ny, nz);
+        float mx, my;
+        unpack2(mul2(dxy, pack2(kn, kn)), mx, my);
+        const float nx = fadd(ox, mx), ny = fadd(oy, my), nz = fadd(oz, fmul(dz, kn));
+        float vx, vy;
+        unpack2(mul2(add2(pack2(nx, ny), one2), hxy), vx, vy);
+        const float vz = fmul(fadd(nz, 1.0f), vs.hz);
+        uint32_t ix = __float2uint_rz(vx), iy = __float2uint_rz(vy), iz = __float2uint_rz(vz);
+        if (CLAMP) { ix = min(ix, a.nx1); iy = min(iy, a.ny1); iz = min(iz, a.nz1); }
+        const uint32_t sn = fetch_voxel<SAMPLER>(a, ix, iy, iz);
         float4 c = lut_fetch(lut_addr, s);  // lut[s] == transfer_fn[s / TF_RATIO]
         if (COUNT) cnt.samples++;
         if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
-            const float vx = fsub(a.lx, px), vy = fsub(a.ly, py), vz = fsub(a.lz, pz);
-            const float len2 = fadd(fadd(fmul(vx, vx), fmul(vy, vy)), fmul(vz, vz));
+            const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
+            const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
             const float inv = fdiv(1.0f, __fsqrt_rn(len2));
-            const float qx = fadd(px, fmul(fmul(vx, inv), 0.01f));
-            const float qy = fadd(py, fmul(fmul(vy, inv), 0.01f));
-            const float qz = fadd(pz, fmul(fmul(vz, inv), 0.01f));
+            const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
+            const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
+            const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
             const uint32_t sl = sample_volume<SAMPLER, true>(a, vs, qx, qy, qz);  // may leave the cube: always clamped
             const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s, 255.0f)), a.kd);
             c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
             if (COUNT) cnt.shaded++;
         }
+        // acc = acc + c * (1 - acc.a): packed products, scalar accumulation
         const float t = fsub(1.0f, aa);
-        ar = fadd(ar, fmul(c.x, t)); ag = fadd(ag, fmul(c.y, t)); ab = fadd(ab, fmul(c.z, t)); aa = fadd(aa, fmul(c.w, t));
+        const f32x2 t2 = pack2(t, t);
+        float qr, qg, qb, qa;
+        unpack2(mul2(pack2(c.x, c.y), t2), qr, qg);
+        unpack2(mul2(pack2(c.z, c.w), t2), qb, qa);
+        ar = fadd(ar, qr); ag = fadd(ag, qg); ab = fadd(ab, qb); aa = fadd(aa, qa);
         if (aa > threshold) break;   // early ray termination, strict >
         if (!(kn <= k_far)) break;   // while (k <= k_far)
         k = kn; px = nx; py = ny; pz = nz; s = sn;
