@@ -20,8 +20,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libvr5.so")
 CSRC = os.path.join(HERE, "csrc")
 
-SAMPLER_LINEAR, SAMPLER_BRICK, SAMPLER_TEX3D = 0, 1, 2
-SAMPLERS = {"linear": 0, "brick": 1, "tex3d": 2}
+SAMPLER_LINEAR, SAMPLER_BRICK, SAMPLER_TEX3D, SAMPLER_HYBRID = 0, 1, 2, 3
+SAMPLERS = {"linear": 0, "brick": 1, "tex3d": 2, "hybrid": 3}
 
 
 class Vr5Error(RuntimeError):

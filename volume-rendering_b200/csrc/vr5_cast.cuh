@@ -41,6 +41,8 @@ struct KArgs {
     float hx, hy, hz;        // dims * 0.5f: (p + 1) * 0.5f * n == (p + 1) * (0.5f * n) exactly (power-of-two scaling)
     uint32_t sx;             // linear: row stride; brick: bricks per row
     uint64_t sxy;            // linear: slice stride; brick: bricks per slab
+    const uint8_t *vol_pad;  // x-fastest grid padded by one replicated voxel per axis (unclamped LDG path), or NULL
+    uint32_t psx, psxy;      // its row / slice strides
     float mbx, mby, mbz;     // min_bound
     // march (RaycasterBase.h:24-30)
     float step, threshold;
@@ -92,6 +94,20 @@ __device__ __forceinline__ uint32_t fetch_voxel<0>(const KArgs &a, uint32_t ix, 
     return __ldg(a.vol + ((uint64_t)iz * a.sxy + (iy * a.sx + ix)));
 }
 
+// x-fastest array padded by one replicated voxel per axis (row stride a.psx, slice stride a.psxy < 2^32): three integer
+// instructions of addressing (IMAD, 2 x IMAD.WIDE) and no clamp. Used by the unclamped linear sampler and by the LDG
+// lanes of the hybrid sampler.
+__device__ __forceinline__ uint32_t fetch_padded(const KArgs &a, uint32_t ix, uint32_t iy, uint32_t iz) {
+    uint32_t v;
+    asm("{\n\t.reg .u32 t;\n\t.reg .u64 p;\n\t"
+        "mad.lo.u32 t, %2, %5, %1;\n\t"
+        "mad.wide.u32 p, %3, %6, %4;\n\t"
+        "mad.wide.u32 p, t, 1, p;\n\t"
+        "ld.global.nc.u8 %0, [p];\n\t}"
+        : "=r"(v) : "r"(ix), "r"(iy), "r"(iz), "l"(a.vol_pad), "r"(a.psx), "r"(a.psxy));
+    return v;
+}
+
 // 8x4x4 bricks: byte offset inside a brick = x0 x1 | y0 y1 | z0 || x2 | z1  (32-B sector = 4x4x2 voxels)
 template <>
 __device__ __forceinline__ uint32_t fetch_voxel<1>(const KArgs &a, uint32_t ix, uint32_t iy, uint32_t iz) {
@@ -124,7 +140,7 @@ __device__ __forceinline__ uint32_t sample_volume(const KArgs &a, const VolScale
         iy = __float2uint_rz(fmul(fadd(py, 1.0f), v.hy));
         ix = __float2uint_rz(fmul(fadd(px, 1.0f), v.hx));
     }
-    return fetch_voxel<SAMPLER>(a, ix, iy, iz);
+    return (SAMPLER == 0 && !CLAMP) ? fetch_padded(a, ix, iy, iz) : fetch_voxel<SAMPLER>(a, ix, iy, iz);
 }
 
 // Loop-invariant kernel parameters are bounced through shared memory once per CTA and read back with volatile loads:
@@ -151,6 +167,8 @@ __device__ __forceinline__ float4 lut_fetch(uint32_t lut_addr, uint32_t s) {
 __device__ __forceinline__ uint32_t div_block(const KArgs &a, uint32_t idx) {
     return a.bd_is_one ? idx : __umulhi(idx, a.bd_magic);
 }
+
+template <int V> struct FetchTag { static constexpr int value = V; };
 
 // ---- one ray (CPURenderer.cpp:11-41). Returns the packed RGBA8 pixel; 0 when the reference leaves it cleared. ----
 template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
@@ -223,8 +241,11 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
     if (!(k <= k_far)) return 0u;  // NaN interval: the reference writes an all-zero pixel
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
     const f32x2 dxy = pack2(dx, dy), hxy = pack2(vs.hx, vs.hy), one2 = pack2(1.0f, 1.0f);
-    uint32_t s = sample_volume<SAMPLER, CLAMP>(a, vs, px, py, pz);
-    for (;;) {
+    constexpr int S0 = SAMPLER >= 3 ? 2 : SAMPLER;  // hybrid: first sample and shading samples come from the texture
+    uint32_t s = sample_volume<S0, CLAMP>(a, vs, px, py, pz);
+    // one march step; FETCH selects the memory path of the PREFETCHED voxel (2 = texture, 0 = linear / padded linear)
+    auto march = [&](auto fetch_tag) -> bool {
+        constexpr int FETCH = decltype(fetch_tag)::value;
         // next point: o + d*kn, then (p + 1) * (n/2) per axis; x,y packed, z scalar; packed products feed scalar adds
         const float kn = fadd(k, step);
         float mx, my;
@@ -235,7 +256,7 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
         const float vz = fmul(fadd(nz, 1.0f), vs.hz);
         uint32_t ix = __float2uint_rz(vx), iy = __float2uint_rz(vy), iz = __float2uint_rz(vz);
         if (CLAMP) { ix = min(ix, a.nx1); iy = min(iy, a.ny1); iz = min(iz, a.nz1); }
-        const uint32_t sn = fetch_voxel<SAMPLER>(a, ix, iy, iz);
+        const uint32_t sn = (FETCH == 0 && !CLAMP) ? fetch_padded(a, ix, iy, iz) : fetch_voxel<FETCH>(a, ix, iy, iz);
         float4 c = lut_fetch(lut_addr, s);  // lut[s] == transfer_fn[s / TF_RATIO]
         if (COUNT) cnt.samples++;
         if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
@@ -245,7 +266,7 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
             const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
             const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
             const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
-            const uint32_t sl = sample_volume<SAMPLER, true>(a, vs, qx, qy, qz);  // may leave the cube: always clamped
+            const uint32_t sl = sample_volume<S0, true>(a, vs, qx, qy, qz);  // may leave the cube: always clamped
             const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s, 255.0f)), a.kd);
             c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
             if (COUNT) cnt.shaded++;
@@ -257,9 +278,22 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
         unpack2(mul2(pack2(c.x, c.y), t2), qr, qg);
         unpack2(mul2(pack2(c.z, c.w), t2), qb, qa);
         ar = fadd(ar, qr); ag = fadd(ag, qg); ab = fadd(ab, qb); aa = fadd(aa, qa);
-        if (aa > threshold) break;   // early ray termination, strict >
-        if (!(kn <= k_far)) break;   // while (k <= k_far)
+        if (aa > threshold) return true;   // early ray termination, strict >
+        if (!(kn <= k_far)) return true;   // while (k <= k_far)
         k = kn; px = nx; py = ny; pz = nz; s = sn;
+        return false;
+    };
+    if (SAMPLER == 3) {
+        // hybrid: prefetches alternate between the texture pipe and the LSU pipe (padded linear array). A warp-wide TLD
+        // costs 8 TEX wavefronts, which made the texture pipe the limiter (79 % busy, profiles/r01_v3_*); 1:1 measured
+        // best against 2:1 and 1:2 (0.647 / 0.706 / 0.716 ms per C3 frame).
+        for (;;) {
+            if (march(FetchTag<2>())) break;
+            if (march(FetchTag<0>())) break;
+        }
+    } else {
+        for (;;)
+            if (march(FetchTag<S0>())) break;
     }
     // Raycaster::write_color (RaycasterBase.h:44-50)
     return trunc_clamp(fmul(ar, 256.0f), 255u) | (trunc_clamp(fmul(ag, 256.0f), 255u) << 8) |

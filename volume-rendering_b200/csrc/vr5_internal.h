@@ -27,6 +27,7 @@ struct vr5_renderer {
     uint32_t nx = 0, ny = 0, nz = 0;
     int sampler = 0;
     uint8_t *d_vol_brick = nullptr;
+    uint8_t *d_vol_padded = nullptr;  // (nx+1)(ny+1)(nz+1), edge replicated: unclamped LDG path
     uint32_t bxn = 0, byn = 0, bzn = 0;
     cudaArray_t d_array = nullptr;
     cudaTextureObject_t tex = 0;
@@ -37,7 +38,7 @@ struct vr5_renderer {
     // partition
     int rank = 0, world = 1, packed = 0;
     // bookkeeping
-    int ctas_per_sm[24] = {0};  // occupancy cache per kernel variant
+    int ctas_per_sm[48] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
     void *d_flush = nullptr;
     size_t flush_bytes = 0;

@@ -103,10 +103,11 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     if ((e = cudaMemset(r->d_queue, 0, 2 * sizeof(unsigned))) != cudaSuccess) return bail("cudaMemset queue", e);
     if ((e = cudaMalloc(&r->d_counters, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc counters", e);
     const char *env = getenv("VR5_SAMPLER");
-    r->sampler = VR5_SAMPLER_TEX3D;  // fastest path on B200 (profiles/r01_sampler_choice.md); $VR5_SAMPLER overrides
+    r->sampler = VR5_SAMPLER_HYBRID;  // fastest path on B200 (profiles/r01_sampler_choice.md); $VR5_SAMPLER overrides
     if (env) {
         if (!strcmp(env, "brick") || !strcmp(env, "1")) r->sampler = VR5_SAMPLER_BRICK;
         else if (!strcmp(env, "linear") || !strcmp(env, "0")) r->sampler = VR5_SAMPLER_LINEAR;
+        else if (!strcmp(env, "tex3d") || !strcmp(env, "2")) r->sampler = VR5_SAMPLER_TEX3D;
     }
     *out = r;
     return 0;
@@ -116,6 +117,7 @@ static void free_layouts(vr5_renderer *r) {
     if (r->tex) { cudaDestroyTextureObject(r->tex); r->tex = 0; }
     if (r->d_array) { cudaFreeArray(r->d_array); r->d_array = nullptr; }
     if (r->d_vol_brick) { cudaFree(r->d_vol_brick); r->d_vol_brick = nullptr; }
+    if (r->d_vol_padded) { cudaFree(r->d_vol_padded); r->d_vol_padded = nullptr; }
 }
 
 extern "C" void vr5_destroy(vr5_renderer *r) {
@@ -160,9 +162,26 @@ extern "C" int vr5_set_transfer_fn(vr5_renderer *r, const float *tf, const uint3
     return 0;
 }
 
+// (nx+1)(ny+1)(nz+1) copy with the last voxel of every axis replicated; 0 on success
+static int build_padded(vr5_renderer *r) {
+    const uint64_t bytes = (uint64_t)(r->nx + 1) * (r->ny + 1) * (r->nz + 1);
+    cudaError_t e = cudaMalloc(&r->d_vol_padded, bytes);
+    if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc padded volume", e, __FILE__, __LINE__); cudaGetLastError(); r->d_vol_padded = nullptr; return 1; }
+    pad_edge_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, r->d_vol_padded, r->nx, r->ny, r->nz);
+    r->launches++;
+    VR5_CUDA(r, cudaGetLastError());
+    return 0;
+}
+
 static int build_layout(vr5_renderer *r) {
     free_layouts(r);
     if (!r->d_vol_linear) return 0;
+    // the unclamped LDG path needs the slice stride of the padded grid in 32 bits
+    const bool pad_ok = (uint64_t)(r->nx + 1) * (r->ny + 1) < (1ull << 32);
+    if ((r->sampler == VR5_SAMPLER_LINEAR || r->sampler >= VR5_SAMPLER_HYBRID) && pad_ok) {
+        if (build_padded(r)) return 1;
+        VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    }
     if (r->sampler == VR5_SAMPLER_BRICK) {
         r->bxn = (r->nx + 7u) / 8u; r->byn = (r->ny + 3u) / 4u; r->bzn = (r->nz + 3u) / 4u;
         const uint64_t bytes = (uint64_t)r->bxn * r->byn * r->bzn * 128u;
@@ -172,16 +191,14 @@ static int build_layout(vr5_renderer *r) {
         r->launches++;
         VR5_CUDA(r, cudaGetLastError());
         VR5_CUDA(r, cudaStreamSynchronize(r->stream));
-    } else if (r->sampler == VR5_SAMPLER_TEX3D) {
+    } else if (r->sampler >= VR5_SAMPLER_TEX3D) {
         cudaChannelFormatDesc desc = cudaCreateChannelDesc(8, 0, 0, 0, cudaChannelFormatKindUnsigned);
         cudaExtent ext = make_cudaExtent(r->nx + 1, r->ny + 1, r->nz + 1);  // one replicated voxel of padding per axis
         cudaError_t e = cudaMalloc3DArray(&r->d_array, &desc, ext, 0);
         if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc3DArray", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
-        uint8_t *d_padded = nullptr;
-        e = cudaMalloc(&d_padded, (uint64_t)(r->nx + 1) * (r->ny + 1) * (r->nz + 1));
-        if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc padded staging volume", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
-        pad_edge_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, d_padded, r->nx, r->ny, r->nz);
-        r->launches++;
+        const bool keep_padded = r->d_vol_padded != nullptr;
+        if (!keep_padded && build_padded(r)) return 1;
+        uint8_t *d_padded = r->d_vol_padded;
         cudaMemcpy3DParms cp;
         memset(&cp, 0, sizeof(cp));
         cp.srcPtr = make_cudaPitchedPtr(d_padded, r->nx + 1, r->nx + 1, r->ny + 1);
@@ -190,7 +207,7 @@ static int build_layout(vr5_renderer *r) {
         cp.kind = cudaMemcpyDeviceToDevice;
         e = cudaMemcpy3DAsync(&cp, r->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
-        cudaFree(d_padded);
+        if (!keep_padded) { cudaFree(r->d_vol_padded); r->d_vol_padded = nullptr; }
         if (e != cudaSuccess) { vr5_fail(r, "3-D texture upload", e, __FILE__, __LINE__); return 1; }
         cudaResourceDesc res;
         memset(&res, 0, sizeof(res));
@@ -261,10 +278,10 @@ extern "C" int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes
 
 extern "C" int vr5_set_sampler(vr5_renderer *r, int sampler) {
     if (!r) return 1;
-    if (sampler < 0 || sampler > 2) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (sampler < 0 || sampler > 3) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
-    if (sampler == r->sampler && (sampler == VR5_SAMPLER_LINEAR || r->d_vol_brick || r->tex)) return 0;
+    if (sampler == r->sampler && (r->d_vol_padded || r->d_vol_brick || r->tex || !r->d_vol_linear)) return 0;
     r->sampler = sampler;
     return build_layout(r);
 }
@@ -290,7 +307,7 @@ extern "C" uint32_t vr5_strip_rows(uint16_t height, int rank, int world) {
 // ---- launch ------------------------------------------------------------------------------------------------------
 template <int S, bool C, bool SH, bool CL>
 static cudaError_t launch_one(vr5_renderer *r, const KArgs &a) {
-    int &per_sm = r->ctas_per_sm[((S * 2 + (C ? 1 : 0)) * 2 + (SH ? 1 : 0)) * 2 + (CL ? 1 : 0)];
+    int &per_sm = r->ctas_per_sm[((S * 2 + (C ? 1 : 0)) * 2 + (SH ? 1 : 0)) * 2 + (CL ? 1 : 0)];  // S < 4
     if (per_sm == 0) {
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cast_kernel<S, C, SH, CL>, kCtaThreads, 0);
         if (e != cudaSuccess) return e;
@@ -334,6 +351,7 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
         a->vol = r->d_vol_linear; a->sx = r->nx; a->sxy = (uint64_t)r->nx * r->ny;
     }
     a->tex = r->tex;
+    a->vol_pad = r->d_vol_padded; a->psx = r->nx + 1; a->psxy = (r->nx + 1) * (r->ny + 1);
     a->mbx = p->min_bound.x; a->mby = p->min_bound.y; a->mbz = p->min_bound.z;
     a->step = p->ray_step; a->threshold = p->ray_threshold;
     a->kd = p->light_kd;
@@ -363,12 +381,14 @@ static int launch(vr5_renderer *r, const KArgs &a, bool count) {
     // shading can only trigger when light_kd > 0.01 (folded into shade_alpha) and some TF entry has alpha > 0.05
     const bool shade = r->tf_can_shade && a.shade_alpha < std::numeric_limits<float>::infinity();
     // the padded texture may be indexed without the upper clamp when rays are clipped to the cube it covers
-    const bool unclamped = r->sampler == VR5_SAMPLER_TEX3D && a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f;
+    // the padded layouts may be indexed without the upper clamp when rays are clipped to the cube they cover
+    const bool cube = a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f;
     cudaError_t e;
     switch (r->sampler) {
-        case VR5_SAMPLER_LINEAR: e = launch_sc<0, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_LINEAR: e = (cube && r->d_vol_padded) ? launch_sc<0, false>(r, a, count, shade) : launch_sc<0, true>(r, a, count, shade); break;
         case VR5_SAMPLER_BRICK: e = launch_sc<1, true>(r, a, count, shade); break;
-        default: e = unclamped ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_HYBRID: e = (cube && r->d_vol_padded) ? launch_sc<3, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
+        default: e = cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
     }
     r->parity ^= 1;
     if (e != cudaSuccess) { vr5_fail(r, "cast_kernel launch", e, __FILE__, __LINE__); return 1; }
