@@ -55,7 +55,11 @@ typedef struct vr5_counters {
 enum { VR5_SAMPLER_LINEAR = 0,  /* x-fastest linear array, LDG.U8 (the reference's layout, ModelBase.h:18-22) */
        VR5_SAMPLER_BRICK = 1,   /* 8x4x4-voxel bricks (one 128-B line each, 4x4x2 per 32-B sector), LDG.U8 */
        VR5_SAMPLER_TEX3D = 2,   /* cudaArray 3-D texture, integer-coordinate point fetch (TLD) */
-       VR5_SAMPLER_HYBRID = 3 }; /* samples alternate between the 3-D texture (TEX pipe) and a padded linear array (LSU pipe) */
+       VR5_SAMPLER_HYBRID = 3,  /* samples alternate between the 3-D texture (TEX pipe) and a padded linear array (LSU pipe) */
+       VR5_SAMPLER_HYBRID_WINDOW = 4,  /* texture : window layout 1 : 1. Window = doubly padded linear array inside one 4-GiB
+                                        * address window, indexed by float bit patterns (no F2I, 32-bit address arithmetic) */
+       VR5_SAMPLER_WINDOW = 5,         /* window layout only */
+       VR5_SAMPLER_HYBRID_WINDOW2 = 6 }; /* texture : window 1 : 2 */
 
 /* ---- lifecycle ------------------------------------------------------------------------------------------ */
 
@@ -84,9 +88,12 @@ int vr5_set_volume(vr5_renderer *r, const uint8_t *host_data, uint64_t bytes, ui
 int vr5_set_volume_device(vr5_renderer *r, const uint8_t *dev_data, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz);
 /* Copies the linear grid back to the host (tests: hand the oracle the exact bytes the kernel sees). */
 int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes);
-/* Select VR5_SAMPLER_*; re-lays out the current volume if one is set. Default: VR5_SAMPLER_HYBRID (fastest on B200) or $VR5_SAMPLER. */
+/* Select VR5_SAMPLER_*; re-lays out the current volume if one is set. Default: VR5_SAMPLER_HYBRID_WINDOW (fastest on B200) or $VR5_SAMPLER. */
 int vr5_set_sampler(vr5_renderer *r, int sampler);
 int vr5_get_sampler(const vr5_renderer *r);
+/* Memory path the LAST launch actually took: the VR5_SAMPLER_* id of the kernel variant (a window sampler renders a
+ * frame through the clamped texture path when the frame's step could leave the guard margin), -1 before any launch. */
+int vr5_last_variant(const vr5_renderer *r);
 
 /* ---- the hot path ----------------------------------------------------------------------------------------- */
 

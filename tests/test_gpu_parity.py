@@ -14,7 +14,10 @@ import oracle
 from common import POSES, assert_parity, golden_scene, product_scene, sha, tf_by_name
 
 pytestmark = pytest.mark.gpu
-SAMPLERS = ["linear", "brick", "tex3d", "hybrid"]
+# kernel variant ids a sampler policy may run as: the window policies switch to their power-of-two specialisations (7..9)
+# when every volume dimension is a power of two (vr5_cast.cuh)
+VARIANT_OF = {"linear": {0}, "brick": {1}, "tex3d": {2}, "hybrid": {3}, "hybridw": {4, 7}, "window": {5, 8}, "hybridw2": {6, 9}}
+SAMPLERS = ["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2"]
 
 
 def _cases():
@@ -44,6 +47,7 @@ def test_golden_frames(name, sampler, golden, port, volumes, R, gpu):
         want, _ = port.render(sc)
         assert_parity(frame, want, exact=True, what=name)
     assert sha(frame) == case["frame_sha256"]
+    assert gpu.last_variant() in VARIANT_OF[sampler]  # the requested memory path ran, not a fallback
     assert gpu.count(params) == case["counters"]
 
 

@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(HERE, "libvr5.so")
 CSRC = os.path.join(HERE, "csrc")
 
 SAMPLER_LINEAR, SAMPLER_BRICK, SAMPLER_TEX3D, SAMPLER_HYBRID = 0, 1, 2, 3
-SAMPLERS = {"linear": 0, "brick": 1, "tex3d": 2, "hybrid": 3}
+SAMPLERS = {"linear": 0, "brick": 1, "tex3d": 2, "hybrid": 3, "hybridw": 4, "window": 5, "hybridw2": 6}
 
 
 class Vr5Error(RuntimeError):
@@ -85,6 +85,7 @@ def lib() -> C.CDLL:
         "vr5_get_volume": (C.c_int, [vp, u8p, C.c_uint64]),
         "vr5_set_sampler": (C.c_int, [vp, C.c_int]),
         "vr5_get_sampler": (C.c_int, [vp]),
+        "vr5_last_variant": (C.c_int, [vp]),
         "vr5_render": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),
         "vr5_render_raycaster": (C.c_int, [vp, vp, vp, C.c_int]),
         "vr5_render_async": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),

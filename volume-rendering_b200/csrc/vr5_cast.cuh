@@ -17,8 +17,22 @@ namespace vr5 {
 constexpr int kCtaThreads = 256;  // 8 warps; each warp owns one 8x4 pixel tile at a time
 constexpr int kTileW = 8;
 constexpr int kTileH = 4;         // = strip height of the multi-GPU partition
-constexpr int kGroupTilesX = 4;   // queue order: groups of 4x8 tiles (32x32 px) so neighbouring queue slots
-constexpr int kGroupTilesY = 8;   //              touch neighbouring voxels (L1/L2 locality)
+constexpr int kGroupLog2X = 2;    // default queue order: groups of 4x8 tiles (32x32 px) so neighbouring queue slots
+constexpr int kGroupLog2Y = 3;    //                      touch neighbouring voxels (L1/L2 locality)
+constexpr int kWindowGuard = 8;   // guard voxels around the window layout (speculative prefetch reach, see window_ok)
+// 6 resident CTAs per SM (40 registers) measured best for the window variants (44 registers / 5 CTAs: 0.631 ms per C3 frame,
+// 40 / 6: 0.617, 36 / 7: 0.717 - profiles/r01_sampler_choice.md). 0 = no minimum for the others.
+#ifndef VR5_MIN_CTAS
+#define VR5_MIN_CTAS (SAMPLER >= 4 ? 6 : 0)
+#endif
+
+// Kernel variant ids (template parameter SAMPLER): 0..6 are the public VR5_SAMPLER_* policies. 7..9 are the power-of-two
+// specialisations of the three window policies, chosen by the launcher when every volume dimension is a power of two:
+// 7 = texture : window 1 : 1, 8 = window only, 9 = texture : window 1 : 2.
+constexpr int kP2First = 7;
+constexpr int kP2Origin = 8;  // voxel index i lives at window / texture coordinate i + kP2Origin on every axis
+__host__ __device__ constexpr bool is_p2(int s) { return s >= kP2First; }
+__host__ __device__ constexpr int p2_mode(int s) { return s - kP2First; }
 
 struct Counters {
     unsigned long long rays_hit, rays_accum, esl_iters, samples, shaded;
@@ -37,12 +51,19 @@ struct KArgs {
     // volume (ModelBase.h:11-16)
     const uint8_t *vol;      // linear or bricked grid
     cudaTextureObject_t tex; // 3-D texture (VR5_SAMPLER_TEX3D)
+    cudaTextureObject_t tex_p2; // power-of-two variants: texture whose coordinate is voxel index + kP2Origin
     uint32_t nx1, ny1, nz1;  // dims - 1 (index clamp)
     float hx, hy, hz;        // dims * 0.5f: (p + 1) * 0.5f * n == (p + 1) * (0.5f * n) exactly (power-of-two scaling)
     uint32_t sx;             // linear: row stride; brick: bricks per row
     uint64_t sxy;            // linear: slice stride; brick: bricks per slab
     const uint8_t *vol_pad;  // x-fastest grid padded by one replicated voxel per axis (unclamped LDG path), or NULL
     uint32_t psx, psxy;      // its row / slice strides
+    // "window" layout (fetch mode 4): x-fastest grid with one replicated voxel on BOTH sides of every axis plus guard
+    // margins, inside one 4-GiB-aligned address window. The low 32 address bits are bz*wsxy + by*wsx + bx, where
+    // b = float bits of (v + wm) rounded toward zero: no F2I, no 64-bit address arithmetic (vr5_render.cu, build_window).
+    uint32_t whi;            // high 32 bits of every address in the window
+    uint32_t wsx, wsxy;      // row / slice strides
+    float wmx, wmy, wmz;     // 2^23 + per-axis integer offsets that make the additive address constant vanish
     float mbx, mby, mbz;     // min_bound
     // march (RaycasterBase.h:24-30)
     float step, threshold;
@@ -108,6 +129,20 @@ __device__ __forceinline__ uint32_t fetch_padded(const KArgs &a, uint32_t ix, ui
     return v;
 }
 
+// Window layout: the voxel index is the integer part of v (>= -1: the replicated low border stands in for the lower clamp,
+// the replicated high border for the upper one). FADD.RZ against a constant in [2^23, 2^24) leaves floor(v) + const in the
+// mantissa (exact for -2^22 < v < 2^22), so the float's bit pattern is used as the biased index directly.
+__device__ __forceinline__ uint32_t fetch_window(uint32_t whi, uint32_t wsx, uint32_t wsxy, uint32_t bx, uint32_t by, uint32_t bz) {
+    uint32_t v;
+    asm("{\n\t.reg .u32 t;\n\t.reg .u64 p;\n\t"
+        "mad.lo.u32 t, %2, %5, %1;\n\t"
+        "mad.lo.u32 t, %3, %6, t;\n\t"
+        "mov.b64 p, {t, %4};\n\t"
+        "ld.global.nc.u8 %0, [p];\n\t}"
+        : "=r"(v) : "r"(bx), "r"(by), "r"(bz), "r"(whi), "r"(wsx), "r"(wsxy));
+    return v;
+}
+
 // 8x4x4 bricks: byte offset inside a brick = x0 x1 | y0 y1 | z0 || x2 | z1  (32-B sector = 4x4x2 voxels)
 template <>
 __device__ __forceinline__ uint32_t fetch_voxel<1>(const KArgs &a, uint32_t ix, uint32_t iy, uint32_t iz) {
@@ -146,7 +181,8 @@ __device__ __forceinline__ uint32_t sample_volume(const KArgs &a, const VolScale
 // Loop-invariant kernel parameters are bounced through shared memory once per CTA and read back with volatile loads:
 // that pins them in general registers for the whole march. Left alone, ptxas re-reads them from the constant bank
 // through the uniform datapath (LDCU) on every iteration - one issue slot each in an issue-bound loop (profiles/).
-struct Pinned { float hx, hy, hz, step, threshold; };
+struct Pinned { float hx, hy, hz, step, threshold, wmx, wmy, wmz; uint32_t whi, wsx, wsxy; };
+struct Window { float mx, my, mz; uint32_t hi, sx, sxy; };  // the window constants held in registers
 
 // Packed fp32 pairs (sm_100 add/mul.rn.f32x2 -> SASS FADD2 / FMUL2): two IEEE round-to-nearest results per issue slot,
 // bit-identical to the scalar ops. ptxas 12.9 contracts a packed mul feeding a packed add into FFMA2 even with
@@ -172,7 +208,7 @@ template <int V> struct FetchTag { static constexpr int value = V; };
 
 // ---- one ray (CPURenderer.cpp:11-41). Returns the packed RGBA8 pixel; 0 when the reference leaves it cleared. ----
 template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
-__device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs, uint32_t lut_addr, const uint32_t *esl_bits,
+__device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs, const Window &win, uint32_t lut_addr, const uint32_t *esl_bits,
                                              float step, float threshold, int col, int row, Counters &cnt) {
     // View::get_ray (ViewBase.h:23-35)
     const float cx = (float)(col - a.half_w);
@@ -241,7 +277,7 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
     if (!(k <= k_far)) return 0u;  // NaN interval: the reference writes an all-zero pixel
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
     const f32x2 dxy = pack2(dx, dy), hxy = pack2(vs.hx, vs.hy), one2 = pack2(1.0f, 1.0f);
-    constexpr int S0 = SAMPLER >= 3 ? 2 : SAMPLER;  // hybrid: first sample and shading samples come from the texture
+    constexpr int S0 = SAMPLER >= 3 ? 2 : SAMPLER;  // hybrids / window: first sample and shading samples come from the texture
     uint32_t s = sample_volume<S0, CLAMP>(a, vs, px, py, pz);
     // one march step; FETCH selects the memory path of the PREFETCHED voxel (2 = texture, 0 = linear / padded linear)
     auto march = [&](auto fetch_tag) -> bool {
@@ -251,12 +287,48 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
         float mx, my;
         unpack2(mul2(dxy, pack2(kn, kn)), mx, my);
         const float nx = fadd(ox, mx), ny = fadd(oy, my), nz = fadd(oz, fmul(dz, kn));
-        float vx, vy;
-        unpack2(mul2(add2(pack2(nx, ny), one2), hxy), vx, vy);
-        const float vz = fmul(fadd(nz, 1.0f), vs.hz);
-        uint32_t ix = __float2uint_rz(vx), iy = __float2uint_rz(vy), iz = __float2uint_rz(vz);
-        if (CLAMP) { ix = min(ix, a.nx1); iy = min(iy, a.ny1); iz = min(iz, a.nz1); }
-        const uint32_t sn = (FETCH == 0 && !CLAMP) ? fetch_padded(a, ix, iy, iz) : fetch_voxel<FETCH>(a, ix, iy, iz);
+        uint32_t sn;
+        if (FETCH == 5 || FETCH == 6) {
+            // power-of-two dims: (p + 1) * 2^e is exact, so floor((p + 1) * 2^e) + kP2Origin is read straight out of the
+            // mantissa of (p + 1) + (2^(23-e) + kP2Origin * 2^-e) rounded toward zero - no multiply, no F2I.
+            f32x2 bxy;
+            asm("add.rz.f32x2 %0, %1, %2;" : "=l"(bxy) : "l"(add2(pack2(nx, ny), one2)), "l"(pack2(win.mx, win.my)));
+            float bxf, byf;
+            unpack2(bxy, bxf, byf);
+            const uint32_t bx = __float_as_uint(bxf), by = __float_as_uint(byf), bz = __float_as_uint(__fadd_rz(fadd(nz, 1.0f), win.mz));
+            if (FETCH == 5) {  // window: the biased indices ARE the low address bits (the array is placed so that the biases cancel)
+                // (a power-of-two row stride would make this a shift-add, but measured 10 % slower: cache-set aliasing)
+                uint32_t lo;
+                asm("{\n\t.reg .u32 t;\n\tmad.lo.u32 t, %2, %4, %1;\n\tmad.lo.u32 %0, %3, %5, t;\n\t}"
+                    : "=r"(lo) : "r"(bx), "r"(by), "r"(bz), "r"(win.sx), "r"(win.sxy));
+                asm("{\n\t.reg .u64 p;\n\tmov.b64 p, {%1, %2};\n\tld.global.nc.u8 %0, [p];\n\t}" : "=r"(sn) : "r"(lo), "r"(win.hi));
+            } else {           // texture: strip the exponent field, coordinate = index + kP2Origin
+                uint32_t r0, r1, r2, r3;
+                asm("tex.3d.v4.u32.s32 {%0, %1, %2, %3}, [%4, {%5, %6, %7, %8}];"
+                    : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                    : "l"(a.tex_p2), "r"(bx & 0x7fffffu), "r"(by & 0x7fffffu), "r"(bz & 0x7fffffu), "r"(0));
+                sn = r0;
+            }
+        } else if (FETCH == 4) {
+            float vx, vy;
+            unpack2(mul2(add2(pack2(nx, ny), one2), hxy), vx, vy);
+            const float vz = fmul(fadd(nz, 1.0f), vs.hz);
+#ifndef VR5_NO_PACK_RZ
+            float bxf, byf;
+            { f32x2 r; asm("add.rz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pack2(vx, vy)), "l"(pack2(win.mx, win.my))); unpack2(r, bxf, byf); }
+            sn = fetch_window(win.hi, win.sx, win.sxy, __float_as_uint(bxf), __float_as_uint(byf), __float_as_uint(__fadd_rz(vz, win.mz)));
+#else
+            sn = fetch_window(win.hi, win.sx, win.sxy, __float_as_uint(__fadd_rz(vx, win.mx)), __float_as_uint(__fadd_rz(vy, win.my)),
+                              __float_as_uint(__fadd_rz(vz, win.mz)));
+#endif
+        } else {
+            float vx, vy;
+            unpack2(mul2(add2(pack2(nx, ny), one2), hxy), vx, vy);
+            const float vz = fmul(fadd(nz, 1.0f), vs.hz);
+            uint32_t ix = __float2uint_rz(vx), iy = __float2uint_rz(vy), iz = __float2uint_rz(vz);
+            if (CLAMP) { ix = min(ix, a.nx1); iy = min(iy, a.ny1); iz = min(iz, a.nz1); }
+            sn = (FETCH == 0 && !CLAMP) ? fetch_padded(a, ix, iy, iz) : fetch_voxel<(FETCH >= 4 ? 0 : FETCH)>(a, ix, iy, iz);
+        }
         float4 c = lut_fetch(lut_addr, s);  // lut[s] == transfer_fn[s / TF_RATIO]
         if (COUNT) cnt.samples++;
         if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
@@ -283,13 +355,43 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
         k = kn; px = nx; py = ny; pz = nz; s = sn;
         return false;
     };
-    if (SAMPLER == 3) {
+    if (is_p2(SAMPLER)) {
+        if (p2_mode(SAMPLER) == 0) {
+            for (;;) {
+                if (march(FetchTag<6>())) break;
+                if (march(FetchTag<5>())) break;
+            }
+        } else if (p2_mode(SAMPLER) == 1) {
+            for (;;)
+                if (march(FetchTag<5>())) break;
+        } else {
+            for (;;) {
+                if (march(FetchTag<6>())) break;
+                if (march(FetchTag<5>())) break;
+                if (march(FetchTag<5>())) break;
+            }
+        }
+    } else if (SAMPLER == 3) {
         // hybrid: prefetches alternate between the texture pipe and the LSU pipe (padded linear array). A warp-wide TLD
         // costs 8 TEX wavefronts, which made the texture pipe the limiter (79 % busy, profiles/r01_v3_*); 1:1 measured
         // best against 2:1 and 1:2 (0.647 / 0.706 / 0.716 ms per C3 frame).
         for (;;) {
             if (march(FetchTag<2>())) break;
             if (march(FetchTag<0>())) break;
+        }
+    } else if (SAMPLER == 4) {  // texture : window, 1 : 1
+        for (;;) {
+            if (march(FetchTag<2>())) break;
+            if (march(FetchTag<4>())) break;
+        }
+    } else if (SAMPLER == 5) {  // window only
+        for (;;)
+            if (march(FetchTag<4>())) break;
+    } else if (SAMPLER == 6) {  // texture : window, 1 : 2
+        for (;;) {
+            if (march(FetchTag<2>())) break;
+            if (march(FetchTag<4>())) break;
+            if (march(FetchTag<4>())) break;
         }
     } else {
         for (;;)
@@ -304,20 +406,22 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
 // SHADE=false is chosen by the host when no sample can take the shading path (light_kd <= 0.01 or no TF entry with
 // alpha > 0.05), CLAMP=false when the sampler is the padded 3-D texture and min_bound == (-1,-1,-1).
 template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
-__global__ void __launch_bounds__(kCtaThreads) cast_kernel(const __grid_constant__ KArgs a) {
+__global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const __grid_constant__ KArgs a) {
     __shared__ float4 s_lut[256];
     __shared__ uint32_t s_esl[1024];
     __shared__ Pinned s_pinned;
     for (int i = threadIdx.x; i < 256; i += kCtaThreads) s_lut[i] = a.tf[i >> 1];
     for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
     if (blockIdx.x == 0 && threadIdx.x == 0) *a.queue_next = 0u;  // arm the other counter for the next frame
-    if (threadIdx.x == 0) s_pinned = Pinned{a.hx, a.hy, a.hz, a.step, a.threshold};
+    if (threadIdx.x == 0) s_pinned = Pinned{a.hx, a.hy, a.hz, a.step, a.threshold, a.wmx, a.wmy, a.wmz, a.whi, a.wsx, a.wsxy};
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
     const volatile Pinned *pinned = &s_pinned;
     const VolScale vs = {pinned->hx, pinned->hy, pinned->hz};
     const float step = pinned->step, threshold = pinned->threshold;
+    Window win = {0.0f, 0.0f, 0.0f, 0u, 0u, 0u};
+    if (SAMPLER >= 4) win = Window{pinned->wmx, pinned->wmy, pinned->wmz, pinned->whi, pinned->wsx, pinned->wsxy};
     const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_lut);
     Counters cnt = {0, 0, 0, 0, 0};
     for (;;) {
@@ -325,14 +429,14 @@ __global__ void __launch_bounds__(kCtaThreads) cast_kernel(const __grid_constant
         if (lane == 0) q = atomicAdd(a.queue, 1u);
         q = __shfl_sync(0xffffffffu, q, 0);
         if (q >= a.n_queue) break;
-        const uint32_t group = q / (kGroupTilesX * kGroupTilesY), within = q % (kGroupTilesX * kGroupTilesY);
-        const uint32_t tx = (group % a.groups_x) * kGroupTilesX + (within % kGroupTilesX);
-        const uint32_t tyl = (group / a.groups_x) * kGroupTilesY + (within / kGroupTilesX);
+        const uint32_t group = q >> (kGroupLog2X + kGroupLog2Y), within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);
+        const uint32_t tx = ((group % a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
+        const uint32_t tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
         if (tx >= a.tiles_x || tyl >= a.tile_rows_local) continue;
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
         if (col < a.width && row < a.height) {  // ragged right / bottom edge: lanes outside the image idle
-            const uint32_t rgba = cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, vs, lut_addr, s_esl, step, threshold, col, row, cnt);
+            const uint32_t rgba = cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, vs, win, lut_addr, s_esl, step, threshold, col, row, cnt);
             if (!COUNT) {
                 const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
                 reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;

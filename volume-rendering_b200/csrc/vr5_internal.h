@@ -26,8 +26,20 @@ struct vr5_renderer {
     uint64_t vol_bytes = 0;
     uint32_t nx = 0, ny = 0, nz = 0;
     int sampler = 0;
+    int last_variant = -1;  // SAMPLER template id of the last cast_kernel launch
     uint8_t *d_vol_brick = nullptr;
     uint8_t *d_vol_padded = nullptr;  // (nx+1)(ny+1)(nz+1), edge replicated: unclamped LDG path
+    uint8_t *d_vol_window = nullptr;  // window layout (fetch mode 4), NULL when the volume does not fit one 4-GiB window
+    uint32_t win_hi = 0, win_sx = 0, win_sxy = 0;
+    float win_mx = 0, win_my = 0, win_mz = 0;
+    // power-of-two window (driver VMM mapping inside a 4-GiB-aligned reservation) + its texture; p2_wl == 0: not built
+    unsigned long long p2_va = 0, p2_map_addr = 0, p2_handle = 0;
+    size_t p2_va_size = 0, p2_map_size = 0;
+    int p2_wl = 0;                    // 1 = built
+    uint32_t p2_hi = 0, p2_sx = 0, p2_sxy = 0;   // high address half, row / slice strides in bytes
+    float p2_mx = 0, p2_my = 0, p2_mz = 0;
+    cudaArray_t d_array_p2 = nullptr;
+    cudaTextureObject_t tex_p2 = 0;
     uint32_t bxn = 0, byn = 0, bzn = 0;
     cudaArray_t d_array = nullptr;
     cudaTextureObject_t tex = 0;
@@ -38,7 +50,7 @@ struct vr5_renderer {
     // partition
     int rank = 0, world = 1, packed = 0;
     // bookkeeping
-    int ctas_per_sm[48] = {0};  // occupancy cache per kernel variant
+    int ctas_per_sm[256] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
     void *d_flush = nullptr;
     size_t flush_bytes = 0;

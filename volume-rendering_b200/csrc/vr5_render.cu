@@ -1,9 +1,12 @@
 // vr5_render.cu - host side of the C ABI (include/vr5.h): device state, layouts, launches, timing.
 // Replaces the frame drivers of the reference's CUDA renderers (GPURenderer1.cu:65-112, GPURenderer23.cu:55-81,
 // GPURenderer4.cu:89-153) with one renderer that owns all of its device state.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <limits>
+#include <math.h>
+#include <cmath>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -57,6 +60,34 @@ __global__ void pad_edge_kernel(const uint8_t *__restrict__ lin, uint8_t *__rest
     }
 }
 
+// linear -> window layout (fetch mode 4): padded grid sx*sy*(nz+2) with original voxel (x,y,z) at (x+1,y+1,z+1), borders
+// replicated, preceded and followed by `margin` guard bytes that only speculative prefetches can touch
+__global__ void window_layout_kernel(const uint8_t *__restrict__ lin, uint8_t *__restrict__ win, uint64_t margin, uint64_t core, uint32_t sx,
+                                     uint32_t sxy, uint32_t nx, uint32_t ny, uint32_t nz) {
+    const uint64_t n = core + 2 * margin;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint8_t v = 0;
+        if (i >= margin && i < margin + core) {
+            const uint64_t off = i - margin;
+            const int z = (int)(off / sxy) - 1, y = (int)((off % sxy) / sx) - 1, x = (int)(off % sx) - 1;
+            v = lin[((uint64_t)min(max(z, 0), (int)nz - 1) * ny + min(max(y, 0), (int)ny - 1)) * nx + min(max(x, 0), (int)nx - 1)];
+        }
+        win[i] = v;
+    }
+}
+
+// linear -> window of the power-of-two variants: rows of `sx` bytes, slices of `rows` rows, `sz` slices, voxel i at
+// coordinate i + origin on every axis, everything outside the grid replicated from the nearest voxel (clamp)
+__global__ void p2_layout_kernel(const uint8_t *__restrict__ lin, uint8_t *__restrict__ win, uint32_t sx, uint32_t rows, uint32_t sz, int origin,
+                                 uint32_t nx, uint32_t ny, uint32_t nz) {
+    const uint64_t n = (uint64_t)sz * rows * sx;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t row = i / sx;
+        const int x = (int)(i % sx) - origin, y = (int)(row % rows) - origin, z = (int)(row / rows) - origin;
+        win[i] = lin[((uint64_t)min(max(z, 0), (int)nz - 1) * ny + min(max(y, 0), (int)ny - 1)) * nx + min(max(x, 0), (int)nx - 1)];
+    }
+}
+
 __global__ void unpack_strips_kernel(const uint32_t *__restrict__ packed, uint32_t rows_padded, int world, uint32_t width,
                                      uint32_t height, uint32_t *__restrict__ frame) {
     const uint64_t n = (uint64_t)width * height;
@@ -103,14 +134,62 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     if ((e = cudaMemset(r->d_queue, 0, 2 * sizeof(unsigned))) != cudaSuccess) return bail("cudaMemset queue", e);
     if ((e = cudaMalloc(&r->d_counters, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc counters", e);
     const char *env = getenv("VR5_SAMPLER");
-    r->sampler = VR5_SAMPLER_HYBRID;  // fastest path on B200 (profiles/r01_sampler_choice.md); $VR5_SAMPLER overrides
+    r->sampler = VR5_SAMPLER_HYBRID_WINDOW;  // fastest path on B200 (profiles/r01_sampler_choice.md); $VR5_SAMPLER overrides
     if (env) {
         if (!strcmp(env, "brick") || !strcmp(env, "1")) r->sampler = VR5_SAMPLER_BRICK;
         else if (!strcmp(env, "linear") || !strcmp(env, "0")) r->sampler = VR5_SAMPLER_LINEAR;
         else if (!strcmp(env, "tex3d") || !strcmp(env, "2")) r->sampler = VR5_SAMPLER_TEX3D;
+        else if (!strcmp(env, "hybrid") || !strcmp(env, "3")) r->sampler = VR5_SAMPLER_HYBRID;
+        else if (!strcmp(env, "hybridw") || !strcmp(env, "4")) r->sampler = VR5_SAMPLER_HYBRID_WINDOW;
+        else if (!strcmp(env, "window") || !strcmp(env, "5")) r->sampler = VR5_SAMPLER_WINDOW;
+        else if (!strcmp(env, "hybridw2") || !strcmp(env, "6")) r->sampler = VR5_SAMPLER_HYBRID_WINDOW2;
     }
     *out = r;
     return 0;
+}
+
+// ---- power-of-two window (kernel variants >= kP2First) -----------------------------------------------------------------
+// The window array must start at an address whose low 32 bits equal a given constant (so that the float-bit biases of the
+// three indices cancel, see vr5_cast.cuh) and must not cross a 4-GiB boundary. cudaMalloc cannot promise either, so the
+// array is mapped with the driver's virtual-memory API into a 4-GiB-aligned reservation. Entry points are resolved at run
+// time (cudaGetDriverEntryPoint): libvr5.so keeps linking against the runtime only.
+struct VmmApi {
+    CUresult (*reserve)(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*addr_free)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*create)(CUmemGenericAllocationHandle *, size_t, const CUmemAllocationProp *, unsigned long long) = nullptr;
+    CUresult (*release)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*map)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*unmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*set_access)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
+    CUresult (*granularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags) = nullptr;
+    bool ok = false;
+};
+
+static const VmmApi &vmm_api() {
+    static VmmApi api;
+    static bool tried = false;
+    if (tried) return api;
+    tried = true;
+    auto get = [](const char *name, void **fn) {
+        cudaDriverEntryPointQueryResult q;
+        return cudaGetDriverEntryPoint(name, fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess && *fn;
+    };
+    api.ok = get("cuMemAddressReserve", (void **)&api.reserve) && get("cuMemAddressFree", (void **)&api.addr_free) &&
+             get("cuMemCreate", (void **)&api.create) && get("cuMemRelease", (void **)&api.release) && get("cuMemMap", (void **)&api.map) &&
+             get("cuMemUnmap", (void **)&api.unmap) && get("cuMemSetAccess", (void **)&api.set_access) &&
+             get("cuMemGetAllocationGranularity", (void **)&api.granularity);
+    if (!api.ok) cudaGetLastError();
+    return api;
+}
+
+static void free_p2(vr5_renderer *r) {
+    if (r->tex_p2) { cudaDestroyTextureObject(r->tex_p2); r->tex_p2 = 0; }
+    if (r->d_array_p2) { cudaFreeArray(r->d_array_p2); r->d_array_p2 = nullptr; }
+    const VmmApi &v = vmm_api();
+    if (r->p2_map_addr) { v.unmap((CUdeviceptr)r->p2_map_addr, r->p2_map_size); r->p2_map_addr = 0; }
+    if (r->p2_handle) { v.release((CUmemGenericAllocationHandle)r->p2_handle); r->p2_handle = 0; }
+    if (r->p2_va) { v.addr_free((CUdeviceptr)r->p2_va, r->p2_va_size); r->p2_va = 0; }
+    r->p2_wl = 0;
 }
 
 static void free_layouts(vr5_renderer *r) {
@@ -118,6 +197,8 @@ static void free_layouts(vr5_renderer *r) {
     if (r->d_array) { cudaFreeArray(r->d_array); r->d_array = nullptr; }
     if (r->d_vol_brick) { cudaFree(r->d_vol_brick); r->d_vol_brick = nullptr; }
     if (r->d_vol_padded) { cudaFree(r->d_vol_padded); r->d_vol_padded = nullptr; }
+    if (r->d_vol_window) { cudaFree(r->d_vol_window); r->d_vol_window = nullptr; }
+    free_p2(r);
 }
 
 extern "C" void vr5_destroy(vr5_renderer *r) {
@@ -173,12 +254,153 @@ static int build_padded(vr5_renderer *r) {
     return 0;
 }
 
+// Window layout for fetch mode 4 (vr5_cast.cuh, fetch_window). Leaves d_vol_window NULL (not an error) when the volume
+// cannot live inside one 4-GiB address window; the launcher then falls back to the texture path.
+static int build_window(vr5_renderer *r) {
+    uint64_t sx = r->nx + 2 < 32 ? 32 : r->nx + 2, sy = r->ny + 2 < 32 ? 32 : r->ny + 2;  // sxy >= 1024 keeps wmz below 2^23
+    if (const char *e = getenv("VR5_WIN_SX")) { const uint64_t v = strtoull(e, nullptr, 10); if (v >= sx && v <= 65536) sx = v; }  // experiment knob
+    const uint64_t sxy = sx * sy, core = sxy * (r->nz + 2);
+    const uint64_t margin = ((uint64_t)kWindowGuard * (sxy + sx + 1) + 255) & ~255ull;
+    const uint64_t total = core + 2 * margin;
+    if (total >= (1ull << 32)) return 0;
+    uint8_t *held[4] = {nullptr, nullptr, nullptr, nullptr}, *got = nullptr;
+    for (int tries = 0; tries < 4 && !got; tries++) {  // an allocation that straddles a 4-GiB boundary is retried
+        uint8_t *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, total);
+        if (e != cudaSuccess) { cudaGetLastError(); break; }
+        const uint64_t a0 = (uint64_t)(uintptr_t)p;
+        if ((a0 >> 32) == ((a0 + total - 1) >> 32)) got = p; else held[tries] = p;
+    }
+    for (uint8_t *h : held) if (h) cudaFree(h);
+    if (!got) return 0;
+    r->d_vol_window = got;
+    window_layout_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, got, margin, core, (uint32_t)sx, (uint32_t)sxy, r->nx, r->ny, r->nz);
+    r->launches++;
+    VR5_CUDA(r, cudaGetLastError());
+    // biased index b = 0x4B000000 + m + i (bits of (2^23 + m) + v rounded toward zero). Choose mz, my, mx so that
+    // bz*sxy + by*sx + bx == low 32 bits of &window[(iz+1), (iy+1), (ix+1)] with no additive constant left over.
+    const uint32_t B = 0x4B000000u, K = (uint32_t)(sxy + sx + 1), G = 64;  // G: lowest offset, keeps 2^23 + m + v >= 2^23 for guard indices
+    const uint32_t w_lo = (uint32_t)((uint64_t)(uintptr_t)got + margin);
+    const uint32_t t = w_lo + K - B * K - G * K;  // mod 2^32
+    const uint32_t mz = t / (uint32_t)sxy + G, rem = t % (uint32_t)sxy, my = rem / (uint32_t)sx + G, mx = rem % (uint32_t)sx + G;
+    r->win_hi = (uint32_t)(((uint64_t)(uintptr_t)got) >> 32);
+    r->win_sx = (uint32_t)sx; r->win_sxy = (uint32_t)sxy;
+    r->win_mx = (float)(8388608u + mx); r->win_my = (float)(8388608u + my); r->win_mz = (float)(8388608u + mz);
+    // self-check of the modular identity on the eight corners of the index range (-1 .. n)
+    for (int c = 0; c < 8; c++) {
+        const int32_t ix = (c & 1) ? (int32_t)r->nx : -1, iy = (c & 2) ? (int32_t)r->ny : -1, iz = (c & 4) ? (int32_t)r->nz : -1;
+        const uint32_t lo = (B + mz + (uint32_t)iz) * (uint32_t)sxy + (B + my + (uint32_t)iy) * (uint32_t)sx + (B + mx + (uint32_t)ix);
+        const uint32_t want = w_lo + (uint32_t)(iz + 1) * (uint32_t)sxy + (uint32_t)(iy + 1) * (uint32_t)sx + (uint32_t)(ix + 1);
+        if (lo != want || mz + r->nz + 2 * G >= (1u << 23)) {
+            cudaFree(r->d_vol_window); r->d_vol_window = nullptr;
+            vr5_fail(r, "window layout: address identity does not hold", cudaSuccess, __FILE__, __LINE__);
+            return 1;
+        }
+    }
+    return 0;
+}
+
+static int exact_log2(uint32_t n) {
+    for (int e = 0; e < 32; e++) if (n == (1u << e)) return e;
+    return -1;
+}
+
+// Power-of-two window + its texture. Leaves p2_wl == 0 (not an error) when the volume is not eligible: a dimension that is
+// not a power of two, no VMM support, or the required start address too close to 4 GiB.
+static int build_p2(vr5_renderer *r) {
+    const int ex = exact_log2(r->nx), ey = exact_log2(r->ny), ez = exact_log2(r->nz);
+    if (ex < 1 || ey < 1 || ez < 1) return 0;
+    const VmmApi &v = vmm_api();
+    if (!v.ok) return 0;
+    const uint32_t G = kP2Origin;
+    // strides are deliberately NOT powers of two: 1024-byte rows measured 10 % slower than 514-byte ones (cache-set aliasing)
+    uint32_t sx = r->nx + 2 * G + 2;
+    if (const char *e = getenv("VR5_WIN_SX")) { const uint32_t v = (uint32_t)strtoul(e, nullptr, 10); if (v >= r->nx + 2 * G && v <= 65536) sx = v; }  // experiment knob
+    const uint32_t rows = r->ny + 2 * G;
+    const uint32_t sz = r->nz + 2 * G;
+    const uint64_t size = (uint64_t)sz * rows * sx;
+    if (size >= (1ull << 32)) return 0;
+    const uint32_t sxy = rows * sx;
+    // index scale per axis is h = n / 2 = 2^(e-1); magic = 2^(23-(e-1)) + G / h has bit pattern ((150-(e-1)) << 23) + G
+    const uint32_t bx = (uint32_t)(150 - (ex - 1)) << 23, by = (uint32_t)(150 - (ey - 1)) << 23, bz = (uint32_t)(150 - (ez - 1)) << 23;
+    const uint32_t a0_lo = bx + by * sx + bz * sxy;  // mod 2^32: where the array must start inside its 4-GiB window
+    if ((uint64_t)a0_lo + size > (1ull << 32)) return 0;
+    CUmemAllocationProp prop;
+    memset(&prop, 0, sizeof(prop));
+    prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    prop.location.id = r->device;
+    size_t gran = 0;
+    if (v.granularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_MINIMUM) != CUDA_SUCCESS || gran == 0) return 0;
+    CUdeviceptr va = 0;
+    const size_t va_size = 1ull << 32;
+    if (v.reserve(&va, va_size, va_size, 0, 0) != CUDA_SUCCESS) return 0;
+    r->p2_va = va; r->p2_va_size = va_size;
+    if (va & (va_size - 1)) { free_p2(r); return 0; }
+    const uint64_t map_lo = a0_lo & ~(uint64_t)(gran - 1);
+    uint64_t map_hi = ((uint64_t)a0_lo + size + gran - 1) & ~(uint64_t)(gran - 1);
+    if (map_hi > va_size) map_hi = va_size;
+    CUmemGenericAllocationHandle h = 0;
+    if (v.create(&h, map_hi - map_lo, &prop, 0) != CUDA_SUCCESS) { free_p2(r); return 0; }
+    r->p2_handle = h;
+    if (v.map(va + map_lo, map_hi - map_lo, 0, h, 0) != CUDA_SUCCESS) { free_p2(r); return 0; }
+    r->p2_map_addr = va + map_lo; r->p2_map_size = map_hi - map_lo;
+    CUmemAccessDesc acc;
+    memset(&acc, 0, sizeof(acc));
+    acc.location = prop.location;
+    acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    if (v.set_access(va + map_lo, map_hi - map_lo, &acc, 1) != CUDA_SUCCESS) { free_p2(r); return 0; }
+    uint8_t *a0 = reinterpret_cast<uint8_t *>((uintptr_t)(va + a0_lo));
+    p2_layout_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, a0, sx, rows, sz, (int)G, r->nx, r->ny, r->nz);
+    r->launches++;
+    VR5_CUDA(r, cudaGetLastError());
+    r->p2_hi = (uint32_t)((uint64_t)va >> 32);
+    r->p2_mx = ldexpf(1.0f, 23 - (ex - 1)) + ldexpf((float)G, -(ex - 1));
+    r->p2_my = ldexpf(1.0f, 23 - (ey - 1)) + ldexpf((float)G, -(ey - 1));
+    r->p2_mz = ldexpf(1.0f, 23 - (ez - 1)) + ldexpf((float)G, -(ez - 1));
+    uint32_t cx, cy, cz;
+    memcpy(&cx, &r->p2_mx, 4); memcpy(&cy, &r->p2_my, 4); memcpy(&cz, &r->p2_mz, 4);
+    if (cx != bx + G || cy != by + G || cz != bz + G) { free_p2(r); vr5_fail(r, "p2 window: magic constants are not exact", cudaSuccess, __FILE__, __LINE__); return 1; }
+    // texture over the same coordinates (index + G), copied out of the window (pitch 2^wl)
+    cudaChannelFormatDesc desc = cudaCreateChannelDesc(8, 0, 0, 0, cudaChannelFormatKindUnsigned);
+    cudaExtent ext = make_cudaExtent(r->nx + 2 * G, r->ny + 2 * G, r->nz + 2 * G);
+    cudaError_t e = cudaMalloc3DArray(&r->d_array_p2, &desc, ext, 0);
+    if (e != cudaSuccess) { cudaGetLastError(); r->d_array_p2 = nullptr; free_p2(r); return 0; }
+    cudaMemcpy3DParms cp;
+    memset(&cp, 0, sizeof(cp));
+    cp.srcPtr = make_cudaPitchedPtr(a0, sx, r->nx + 2 * G, rows);
+    cp.dstArray = r->d_array_p2;
+    cp.extent = ext;
+    cp.kind = cudaMemcpyDeviceToDevice;
+    e = cudaMemcpy3DAsync(&cp, r->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
+    if (e != cudaSuccess) { free_p2(r); vr5_fail(r, "p2 texture upload", e, __FILE__, __LINE__); return 1; }
+    cudaResourceDesc res;
+    memset(&res, 0, sizeof(res));
+    res.resType = cudaResourceTypeArray;
+    res.res.array.array = r->d_array_p2;
+    cudaTextureDesc td;
+    memset(&td, 0, sizeof(td));
+    td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+    td.filterMode = cudaFilterModePoint;
+    td.readMode = cudaReadModeElementType;
+    td.normalizedCoords = 0;
+    VR5_CUDA(r, cudaCreateTextureObject(&r->tex_p2, &res, &td, nullptr));
+    r->p2_wl = 1; r->p2_sx = sx; r->p2_sxy = sxy;
+    return 0;
+}
+
 static int build_layout(vr5_renderer *r) {
     free_layouts(r);
     if (!r->d_vol_linear) return 0;
+    if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW) {
+        if (!getenv("VR5_NO_P2") && build_p2(r)) return 1;
+        if (!r->p2_wl && build_window(r)) return 1;
+        VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    }
     // the unclamped LDG path needs the slice stride of the padded grid in 32 bits
     const bool pad_ok = (uint64_t)(r->nx + 1) * (r->ny + 1) < (1ull << 32);
-    if ((r->sampler == VR5_SAMPLER_LINEAR || r->sampler >= VR5_SAMPLER_HYBRID) && pad_ok) {
+    if ((r->sampler == VR5_SAMPLER_LINEAR || r->sampler == VR5_SAMPLER_HYBRID) && pad_ok) {
         if (build_padded(r)) return 1;
         VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     }
@@ -278,14 +500,15 @@ extern "C" int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes
 
 extern "C" int vr5_set_sampler(vr5_renderer *r, int sampler) {
     if (!r) return 1;
-    if (sampler < 0 || sampler > 3) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (sampler < 0 || sampler > VR5_SAMPLER_HYBRID_WINDOW2) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
-    if (sampler == r->sampler && (r->d_vol_padded || r->d_vol_brick || r->tex || !r->d_vol_linear)) return 0;
+    if (sampler == r->sampler && (r->d_vol_padded || r->d_vol_brick || r->tex || r->d_vol_window || r->p2_wl || !r->d_vol_linear)) return 0;
     r->sampler = sampler;
     return build_layout(r);
 }
 extern "C" int vr5_get_sampler(const vr5_renderer *r) { return r ? r->sampler : -1; }
+extern "C" int vr5_last_variant(const vr5_renderer *r) { return r ? r->last_variant : -1; }
 
 extern "C" int vr5_set_partition(vr5_renderer *r, int rank, int world, int packed) {
     if (!r) return 1;
@@ -307,7 +530,7 @@ extern "C" uint32_t vr5_strip_rows(uint16_t height, int rank, int world) {
 // ---- launch ------------------------------------------------------------------------------------------------------
 template <int S, bool C, bool SH, bool CL>
 static cudaError_t launch_one(vr5_renderer *r, const KArgs &a) {
-    int &per_sm = r->ctas_per_sm[((S * 2 + (C ? 1 : 0)) * 2 + (SH ? 1 : 0)) * 2 + (CL ? 1 : 0)];  // S < 4
+    int &per_sm = r->ctas_per_sm[((S * 2 + (C ? 1 : 0)) * 2 + (SH ? 1 : 0)) * 2 + (CL ? 1 : 0)];  // S < 8
     if (per_sm == 0) {
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cast_kernel<S, C, SH, CL>, kCtaThreads, 0);
         if (e != cudaSuccess) return e;
@@ -318,6 +541,7 @@ static cudaError_t launch_one(vr5_renderer *r, const KArgs &a) {
     if (grid > needed) grid = needed ? needed : 1;
     cast_kernel<S, C, SH, CL><<<grid, kCtaThreads, 0, r->stream>>>(a);
     r->launches++;
+    r->last_variant = S;
     return cudaGetLastError();
 }
 
@@ -352,6 +576,8 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     }
     a->tex = r->tex;
     a->vol_pad = r->d_vol_padded; a->psx = r->nx + 1; a->psxy = (r->nx + 1) * (r->ny + 1);
+    a->whi = r->win_hi; a->wsx = r->win_sx; a->wsxy = r->win_sxy;
+    a->wmx = r->win_mx; a->wmy = r->win_my; a->wmz = r->win_mz;
     a->mbx = p->min_bound.x; a->mby = p->min_bound.y; a->mbz = p->min_bound.z;
     a->step = p->ray_step; a->threshold = p->ray_threshold;
     a->kd = p->light_kd;
@@ -368,26 +594,75 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     a->tiles_x = (a->width + kTileW - 1) / kTileW;
     const uint32_t strips = (a->height + kTileH - 1) / kTileH;
     a->tile_rows_local = (uint32_t)r->rank < strips ? (strips - r->rank + r->world - 1) / r->world : 0;
-    a->groups_x = (a->tiles_x + kGroupTilesX - 1) / kGroupTilesX;
-    const uint32_t groups_y = (a->tile_rows_local + kGroupTilesY - 1) / kGroupTilesY;
-    a->n_queue = a->groups_x * groups_y * (kGroupTilesX * kGroupTilesY);
+    a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
+    const uint32_t groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
+    a->n_queue = (a->groups_x * groups_y) << (kGroupLog2X + kGroupLog2Y);
     a->queue = r->d_queue + r->parity;
     a->queue_next = r->d_queue + (r->parity ^ 1);
     a->counters = reinterpret_cast<Counters *>(r->d_counters);
     return 0;
 }
 
-static int launch(vr5_renderer *r, const KArgs &a, bool count) {
+// The window path has no index clamp: its prefetch runs one step past the clip interval, so that step must stay inside the
+// guard margin (kWindowGuard voxels) on every axis for every ray of the frame. d is affine in the pixel position, so the
+// four image corners bound it. Anything non-finite or out of range renders through the clamped texture path instead.
+static bool window_ok(const vr5_renderer *r, const KArgs &a) {
+    if (!r->d_vol_window && !r->p2_wl) return false;
+    const float lim = (float)((r->p2_wl ? kP2Origin : kWindowGuard) - 2);
+    const float hx = a.hx, hy = a.hy, hz = a.hz;
+    if (!(a.step > 0.0f) || !std::isfinite(a.step)) return false;
+    for (int c = 0; c < 4; c++) {
+        float dx = a.dx, dy = a.dy, dz = a.dz;
+        if (a.perspective) {
+            const float cx = (c & 1) ? (float)(a.width - 1 - a.half_w) : (float)(-a.half_w);
+            const float cy = (c & 2) ? (float)(a.height - 1 - a.half_h) : (float)(-a.half_h);
+            dx += a.rx * cx + a.ux * cy; dy += a.ry * cx + a.uy * cy; dz += a.rz * cx + a.uz * cy;
+        }
+        const float ex = fabsf(dx) * a.step * hx, ey = fabsf(dy) * a.step * hy, ez = fabsf(dz) * a.step * hz;
+        if (!(ex <= lim) || !(ey <= lim) || !(ez <= lim)) return false;  // also rejects NaN
+    }
+    const float o[12] = {a.ox, a.oy, a.oz, a.rx, a.ry, a.rz, a.ux, a.uy, a.uz, a.dx, a.dy, a.dz};
+    for (float v : o) if (!std::isfinite(v)) return false;
+    return true;
+}
+
+template <int ID>
+static cudaError_t launch_p2_id(vr5_renderer *r, const KArgs &a, bool shade) {
+    return shade ? launch_one<ID, false, true, false>(r, a) : launch_one<ID, false, false, false>(r, a);
+}
+
+static cudaError_t launch_p2(vr5_renderer *r, const KArgs &a, bool shade, int mode) {
+    switch (mode) {
+        case 0: return launch_p2_id<kP2First + 0>(r, a, shade);
+        case 1: return launch_p2_id<kP2First + 1>(r, a, shade);
+        case 2: return launch_p2_id<kP2First + 2>(r, a, shade);
+    }
+    return cudaErrorInvalidValue;
+}
+
+static int launch(vr5_renderer *r, KArgs a, bool count) {
     // shading can only trigger when light_kd > 0.01 (folded into shade_alpha) and some TF entry has alpha > 0.05
     const bool shade = r->tf_can_shade && a.shade_alpha < std::numeric_limits<float>::infinity();
     // the padded texture may be indexed without the upper clamp when rays are clipped to the cube it covers
     // the padded layouts may be indexed without the upper clamp when rays are clipped to the cube they cover
     const bool cube = a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f;
     cudaError_t e;
+    // power-of-two specialisation of the window policies (the instrumented variant counts through the generic kernels:
+    // work counters do not depend on the memory path)
+    if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW && r->p2_wl && !count && cube && window_ok(r, a)) {
+        a.whi = r->p2_hi; a.wmx = r->p2_mx; a.wmy = r->p2_my; a.wmz = r->p2_mz; a.tex_p2 = r->tex_p2; a.wsx = r->p2_sx; a.wsxy = r->p2_sxy;
+        e = launch_p2(r, a, shade, r->sampler - VR5_SAMPLER_HYBRID_WINDOW);
+        r->parity ^= 1;
+        if (e != cudaSuccess) { vr5_fail(r, "cast_kernel launch", e, __FILE__, __LINE__); return 1; }
+        return 0;
+    }
     switch (r->sampler) {
         case VR5_SAMPLER_LINEAR: e = (cube && r->d_vol_padded) ? launch_sc<0, false>(r, a, count, shade) : launch_sc<0, true>(r, a, count, shade); break;
         case VR5_SAMPLER_BRICK: e = launch_sc<1, true>(r, a, count, shade); break;
         case VR5_SAMPLER_HYBRID: e = (cube && r->d_vol_padded) ? launch_sc<3, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_HYBRID_WINDOW: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<4, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_WINDOW: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<5, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_HYBRID_WINDOW2: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<6, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         default: e = cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
     }
     r->parity ^= 1;

@@ -163,6 +163,10 @@ class GPURenderer5:
         s = SAMPLERS[sampler] if isinstance(sampler, str) else int(sampler)
         self._check(self._L.vr5_set_sampler(self._h, s))
 
+    def last_variant(self) -> int:
+        """VR5_SAMPLER_* id of the kernel variant the last launch used (see vr5_last_variant)."""
+        return self._L.vr5_last_variant(self._h)
+
     def synth_volume(self, kind: int, n: int, seed: int):
         self._check(self._L.vr5_synth_volume(self._h, kind, n, seed))
 
