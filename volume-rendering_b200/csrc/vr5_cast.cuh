@@ -19,6 +19,10 @@ constexpr int kTileW = 8;
 constexpr int kTileH = 4;         // = strip height of the multi-GPU partition
 constexpr int kGroupLog2X = 2;    // default queue order: groups of 4x8 tiles (32x32 px) so neighbouring queue slots
 constexpr int kGroupLog2Y = 3;    //                      touch neighbouring voxels (L1/L2 locality)
+// Software-pipeline depth of the march loop: the voxel of sample i + 1 is requested before sample i is composited. A depth
+// of 2 was tried (C3: 0.630 ms against 0.616 ms at depth 1 - two register moves per iteration, no fewer long-scoreboard
+// stalls) and dropped; reach_ok() in vr5_render.cu scales the speculative reach with it.
+constexpr int kPrefetch = 1;
 constexpr int kWindowGuard = 8;   // guard voxels around the window layout (speculative prefetch reach, see window_ok)
 // 6 resident CTAs per SM (40 registers) measured best for the window variants (44 registers / 5 CTAs: 0.631 ms per C3 frame,
 // 40 / 6: 0.617, 36 / 7: 0.717 - profiles/r01_sampler_choice.md). 0 = no minimum for the others.

@@ -245,7 +245,8 @@ extern "C" int vr5_set_transfer_fn(vr5_renderer *r, const float *tf, const uint3
 
 // (nx+1)(ny+1)(nz+1) copy with the last voxel of every axis replicated; 0 on success
 static int build_padded(vr5_renderer *r) {
-    const uint64_t bytes = (uint64_t)(r->nx + 1) * (r->ny + 1) * (r->nz + 1);
+    // + kWindowGuard slices, rows and bytes of tail: the unclamped LDG path prefetches past the clip interval (reach_ok)
+    const uint64_t bytes = (uint64_t)(r->nx + 1) * (r->ny + 1) * (r->nz + 1) + (uint64_t)kWindowGuard * ((uint64_t)(r->nx + 1) * (r->ny + 1) + (r->nx + 1) + 1);
     cudaError_t e = cudaMalloc(&r->d_vol_padded, bytes);
     if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc padded volume", e, __FILE__, __LINE__); cudaGetLastError(); r->d_vol_padded = nullptr; return 1; }
     pad_edge_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, r->d_vol_padded, r->nx, r->ny, r->nz);
@@ -606,9 +607,15 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
 // The window path has no index clamp: its prefetch runs one step past the clip interval, so that step must stay inside the
 // guard margin (kWindowGuard voxels) on every axis for every ray of the frame. d is affine in the pixel position, so the
 // four image corners bound it. Anything non-finite or out of range renders through the clamped texture path instead.
+static bool reach_ok(const KArgs &a, float lim);
 static bool window_ok(const vr5_renderer *r, const KArgs &a) {
     if (!r->d_vol_window && !r->p2_wl) return false;
-    const float lim = (float)((r->p2_wl ? kP2Origin : kWindowGuard) - 2);
+    return reach_ok(a, (float)((r->p2_wl ? kP2Origin : kWindowGuard) - 2));
+}
+
+// true when no prefetch of the frame (kPrefetch steps past the clip interval) can move more than `lim` voxels on any axis
+static bool reach_ok(const KArgs &a, float lim) {
+    lim /= (float)kPrefetch;
     const float hx = a.hx, hy = a.hy, hz = a.hz;
     if (!(a.step > 0.0f) || !std::isfinite(a.step)) return false;
     for (int c = 0; c < 4; c++) {
@@ -657,9 +664,9 @@ static int launch(vr5_renderer *r, KArgs a, bool count) {
         return 0;
     }
     switch (r->sampler) {
-        case VR5_SAMPLER_LINEAR: e = (cube && r->d_vol_padded) ? launch_sc<0, false>(r, a, count, shade) : launch_sc<0, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_LINEAR: e = (cube && r->d_vol_padded && reach_ok(a, (float)(kWindowGuard - 2))) ? launch_sc<0, false>(r, a, count, shade) : launch_sc<0, true>(r, a, count, shade); break;
         case VR5_SAMPLER_BRICK: e = launch_sc<1, true>(r, a, count, shade); break;
-        case VR5_SAMPLER_HYBRID: e = (cube && r->d_vol_padded) ? launch_sc<3, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_HYBRID: e = (cube && r->d_vol_padded && reach_ok(a, (float)(kWindowGuard - 2))) ? launch_sc<3, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         case VR5_SAMPLER_HYBRID_WINDOW: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<4, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         case VR5_SAMPLER_WINDOW: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<5, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         case VR5_SAMPLER_HYBRID_WINDOW2: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<6, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
