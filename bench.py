@@ -22,6 +22,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries exactly one JSON line: NCCL's version banner (NCCL_DEBUG=VERSION/INFO prints to stdout) would break that
+if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE") and not os.environ.get("NCCL_DEBUG_FILE"):
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 WORKLOADS = {  # BASELINE.json configs[1..4]
     "c2": dict(kind=0, n=256, seed=1, tf="semi", w=1920, h=1080, name="synthA 256^3 uint8, semi TF, 1920x1080, 360-frame orbit"),
@@ -250,7 +253,6 @@ def run_b200_arm(args, wl):
     scene = R.Scene(None, tf, R.build_esl_bits(tf, mm), bd, bs, R.default_ray_step(n, n, n))
     gpu.set_transfer_fn(scene.tf, scene.esl_bits)
     gpu.set_window_buffer(w, h)
-    gpu.set_partition(rank, world, world > 1)
 
     def params_for(i, steps):
         _, ang = orbit_angles(i, steps)
@@ -259,18 +261,38 @@ def run_b200_arm(args, wl):
     frames = [params_for(i, args.steps) for i in range(args.steps)]
     warm = [params_for(i * 7 + 3, ORBIT_FRAMES) for i in range(max(args.warmup, 3))]
 
+    # N > 1: "peer" = every rank's kernel stores its pixels straight into rank 0's frame ring over NVLink (fused render +
+    # gather, csrc/vr5_peer.cu); "nccl" = packed strips + dist.gather + unpack kernel (the plain-collective baseline)
+    gather = args.gather if world > 1 else "none"
+    gpu.set_partition(rank, world, world > 1 and gather == "nccl")
+    PEER_SLOTS = 4
+    if gather == "peer":
+        box = [gpu.peer_create(PEER_SLOTS) if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            gpu.peer_open(box[0], PEER_SLOTS)
+        dist.barrier()
+    seq = [0]
+
     L = R.lib()
     rows_padded = max(L.vr5_strip_rows(h, r, world) for r in range(world))
     frame_dev = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
-    packed = torch.empty((rows_padded, w, 4), dtype=torch.uint8, device=dev) if world > 1 else None
-    gathered = torch.empty((world, rows_padded, w, 4), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None
+    packed = torch.empty((rows_padded, w, 4), dtype=torch.uint8, device=dev) if gather == "nccl" else None
+    gathered = torch.empty((world, rows_padded, w, 4), dtype=torch.uint8, device=dev) if (gather == "nccl" and rank == 0) else None
     pinned = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+    pinned_np = pinned.numpy() if rank == 0 else None
 
     def step_device(p):
         """One frame, device resident: N=1 renders in place; N>1 renders this rank's strips, gathers them to rank 0
         over NCCL and scatters them into the frame there. Everything is enqueued on one stream, no host sync."""
         if world == 1:
             gpu.render_device(p, frame_dev.data_ptr(), blocking=False)
+        elif gather == "peer":
+            gpu.peer_render(p, seq[0])
+            if rank == 0:
+                gpu.peer_wait(seq[0])       # frame complete in the ring (a consumer would read it here)
+                gpu.peer_release(seq[0])
+            seq[0] += 1
         else:
             gpu.render_device(p, packed.data_ptr(), blocking=False)
             dist.gather(packed, list(gathered.unbind(0)) if rank == 0 else None, dst=0)
@@ -281,6 +303,13 @@ def run_b200_arm(args, wl):
         """The call a user makes: frame lands in HOST memory (pinned), blocking, like renderers 1-2 of the reference."""
         if world == 1:
             gpu.render_to_pinned(p, pinned.data_ptr())
+        elif gather == "peer":
+            gpu.peer_render(p, seq[0])
+            if rank == 0:
+                gpu.memcpy_d2h(pinned_np, gpu.peer_wait(seq[0]))   # blocking D2H of the complete frame
+                gpu.peer_release(seq[0])
+            seq[0] += 1
+            stream.synchronize()
         else:
             step_device(p)
             if rank == 0:
@@ -319,13 +348,6 @@ def run_b200_arm(args, wl):
     barrier()
     ms = e0.elapsed_time(e1)
     launches = gpu.launch_count() - launches0
-    # keep the same load running (untimed) until the clock sampler has seen >= 1 s of it
-    t_soak = time.perf_counter()
-    while time.perf_counter() - t_soak < max(0.0, 1.0 - ms / 1e3):
-        for p in frames[: max(1, len(frames) // 4)]:
-            step_device(p)
-        torch.cuda.synchronize(dev)
-    clocks.stop()
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     lt = torch.tensor([launches], dtype=torch.int64, device=dev)
     if world > 1:
@@ -333,6 +355,13 @@ def run_b200_arm(args, wl):
         dist.all_reduce(lt)
     ms = float(t[0])
     launches = int(lt[0])
+    # keep the same load running (untimed) until the clock sampler has seen >= 1 s of it; the number of extra steps is
+    # derived from the reduced time, so every rank runs the same count (the peer ring needs equal frame sequences)
+    soak_steps = int(max(0.0, 1.0 - ms / 1e3) / max(ms / 1e3 / args.steps, 1e-6)) + 1
+    for i in range(soak_steps):
+        step_device(frames[i % len(frames)])
+    torch.cuda.synchronize(dev)
+    clocks.stop()
 
     # -- end to end: host buffers, blocking call per frame, wall clock, max over ranks --------------------------------
     for p in warm[:3]:
@@ -349,7 +378,9 @@ def run_b200_arm(args, wl):
     e2e_s = float(t[0])
 
     # -- dominant kernel alone: per-launch CUDA events on its stream (this rank's share of each frame) ---------------
-    out_ptr = frame_dev.data_ptr() if world == 1 else packed.data_ptr()
+    out_ptr = packed.data_ptr() if gather == "nccl" else frame_dev.data_ptr()
+    if gather == "peer":
+        gpu.peer_status()   # raises if any device-side wait timed out
     k_ms = gpu.render_timed(frames, out_ptr, l2_flush=False)
     k_ms_flushed = gpu.render_timed(frames[: min(len(frames), 24)], out_ptr, l2_flush=True)
     strip_px = (L.vr5_strip_rows(h, rank, world) if world > 1 else h) * w
@@ -372,7 +403,7 @@ def run_b200_arm(args, wl):
             "dtype": "f32", "data": "synthetic", "fps": args.steps / (ms * 1e-3),
             "config": {"workload": wl["name"], "volume": "%d^3" % n, "viewport": "%dx%d" % (w, h), "tf": wl["tf"],
                        "projection": "orthographic", "sampler": args.sampler, "samples_per_frame": samples_total / args.steps,
-                       "parallelism": "image-space strips x%d, volume replicated, NCCL gather to rank 0" % world if world > 1 else "single GPU",
+                       "parallelism": ("image-space strips x%d, volume replicated, %s" % (world, "pixels stored straight into rank 0's frame ring over NVLink peer memory (fused render + gather)" if gather == "peer" else "NCCL gather to rank 0")) if world > 1 else "single GPU",
                        "l2": "no flush in the timed loop: per frame the kernel reads the %.0f MB volume and writes the %.1f MB frame (L2 is 126 MB); "
                              "the flushed per-kernel time is reported in roofline.kernel_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
@@ -422,6 +453,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how strips reach rank 0")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

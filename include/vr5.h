@@ -141,6 +141,35 @@ uint32_t vr5_strip_rows(uint16_t height, int rank, int world);
  * a full frame. Both pointers are device pointers. */
 int vr5_unpack_strips(vr5_renderer *r, const void *packed_all, uint32_t rows_padded, int world, void *frame_rgba8);
 
+/* ---- fused render + gather over NVLink peer memory (replaces render -> NCCL gather -> unpack) ---- */
+
+/* The gathering rank ("owner") holds a ring of `slots` full frames plus flag words in one device allocation; every other
+ * rank maps it (CUDA IPC) and its ray-cast kernel stores each pixel straight into its final place in the owner's frame
+ * over NVLink. Frames carry a sequence number seq = 0, 1, 2, ... agreed by all ranks; frame seq lives in slot seq % slots.
+ * Flags: arrive[slot] counts writer ranks that finished a frame in that slot; consumed = frames released by the owner.
+ * A writer may store frame seq only after frame seq - slots was released; the owner may read frame seq only after all
+ * world - 1 writers arrived. Both conditions are enforced on the device by one-thread wait kernels (bounded: a wait
+ * that exceeds the timeout sets a status flag instead of hanging). One process per GPU; never two ranks on one GPU. */
+#define VR5_PEER_HANDLE_BYTES 64
+/* owner: allocate the ring for the current window (vr5_set_window first); slots >= 1 */
+int vr5_peer_create(vr5_renderer *r, int slots);
+/* owner: IPC handle of the ring (cudaIpcMemHandle_t, 64 bytes) to be sent to the other ranks by any host transport */
+int vr5_peer_export(vr5_renderer *r, void *handle_out64);
+/* writer: map the owner's ring; `slots` and the window must equal the owner's */
+int vr5_peer_open(vr5_renderer *r, const void *handle64, int slots);
+/* same-process variant (tests; two renderers of one process): share the owner's ring directly */
+int vr5_peer_open_local(vr5_renderer *r, vr5_renderer *owner);
+/* any rank: render this rank's strips (vr5_set_partition, packed = 0) of frame `seq` into the ring, then signal. Async. */
+int vr5_peer_render(vr5_renderer *r, const vr5_params *p, uint64_t seq);
+/* owner: enqueue the wait for all writers of frame `seq`; *frame_dev_out = device pointer of the complete frame, valid
+ * for work enqueued on the renderer's stream after this call and before vr5_peer_release(seq) */
+int vr5_peer_wait(vr5_renderer *r, uint64_t seq, void **frame_dev_out);
+/* owner: frame `seq` is consumed; its slot may be overwritten by frame seq + slots */
+int vr5_peer_release(vr5_renderer *r, uint64_t seq);
+/* 0 = ok, 1 = some device-side wait timed out since vr5_peer_create / vr5_peer_open (synchronises the stream) */
+int vr5_peer_status(vr5_renderer *r);
+void vr5_peer_close(vr5_renderer *r);
+
 /* ---- synthetic volumes generated on the device (bench inputs) ------------------------------- */
 
 /* kind 0 = synthA (dense Marschner-Lobb-like), 1 = synthB (sparse spheres); integer arithmetic, byte-identical to

@@ -102,6 +102,15 @@ def lib() -> C.CDLL:
         "vr5_set_partition": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
         "vr5_strip_rows": (C.c_uint32, [C.c_uint16, C.c_int, C.c_int]),
         "vr5_unpack_strips": (C.c_int, [vp, vp, C.c_uint32, C.c_int, vp]),
+        "vr5_peer_create": (C.c_int, [vp, C.c_int]),
+        "vr5_peer_export": (C.c_int, [vp, vp]),
+        "vr5_peer_open": (C.c_int, [vp, vp, C.c_int]),
+        "vr5_peer_open_local": (C.c_int, [vp, vp]),
+        "vr5_peer_render": (C.c_int, [vp, C.POINTER(Params), C.c_uint64]),
+        "vr5_peer_wait": (C.c_int, [vp, C.c_uint64, C.POINTER(vp)]),
+        "vr5_peer_release": (C.c_int, [vp, C.c_uint64]),
+        "vr5_peer_status": (C.c_int, [vp]),
+        "vr5_peer_close": (None, [vp]),
         "vr5_synth_volume": (C.c_int, [vp, C.c_int, C.c_uint16, C.c_uint32]),
         "vr5_scene_default_base_tf": (None, [f32p]),
         "vr5_scene_premultiply_tf": (None, [f32p, f32p]),

@@ -49,6 +49,12 @@ struct vr5_renderer {
     void *d_counters = nullptr;
     // partition
     int rank = 0, world = 1, packed = 0;
+    // peer ring (vr5_peer.cu): owner allocates, writers map it
+    uint8_t *peer_base = nullptr;     // header (flags) + slots frames
+    bool peer_owner = false, peer_ipc_mapped = false;
+    int peer_slots = 0;
+    size_t peer_frame_stride = 0;
+    uint64_t peer_released = 0;       // owner, host side: frames released so far
     // bookkeeping
     int ctas_per_sm[256] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
@@ -58,6 +64,7 @@ struct vr5_renderer {
 };
 
 void vr5_fail(vr5_renderer *r, const char *what, cudaError_t e, const char *file, int line);
+int vr5_render_into(vr5_renderer *r, const struct vr5_params *p, void *out_dev);  // async launch of the cast kernel, device buffer
 int vr5_adopt_volume(vr5_renderer *r, uint8_t *dev_owned, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz);
 
 #define VR5_CUDA(r, call)                                         \

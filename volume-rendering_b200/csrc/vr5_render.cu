@@ -213,6 +213,7 @@ extern "C" void vr5_destroy(vr5_renderer *r) {
     cudaFree(r->d_queue);
     cudaFree(r->d_counters);
     cudaFree(r->d_flush);
+    vr5_peer_close(r);
     if (r->own_stream) cudaStreamDestroy(r->own_stream);
     delete r;
 }
@@ -701,6 +702,12 @@ static int render_impl(vr5_renderer *r, const vr5_params *p, void *out, int out_
     }
     if (blocking) VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     return 0;
+}
+
+int vr5_render_into(vr5_renderer *r, const vr5_params *p, void *out_dev) {
+    KArgs a;
+    if (fill_args(r, p, out_dev, &a)) return 1;
+    return launch(r, a, false);
 }
 
 extern "C" int vr5_render(vr5_renderer *r, const vr5_params *p, void *out, int out_is_device) { return render_impl(r, p, out, out_is_device, true); }

@@ -205,6 +205,38 @@ class GPURenderer5:
     def unpack_strips(self, packed_ptr, rows_padded, world, frame_ptr):
         self._check(self._L.vr5_unpack_strips(self._h, packed_ptr, rows_padded, world, frame_ptr))
 
+    # -- fused render + gather over peer memory (include/vr5.h) -----------------------------------------------------
+    def peer_create(self, slots: int) -> bytes:
+        """Owner: allocate the frame ring, return its 64-byte IPC handle."""
+        self._check(self._L.vr5_peer_create(self._h, slots))
+        buf = C.create_string_buffer(64)
+        self._check(self._L.vr5_peer_export(self._h, buf))
+        return buf.raw
+
+    def peer_open(self, handle: bytes, slots: int):
+        buf = C.create_string_buffer(handle, 64)
+        self._check(self._L.vr5_peer_open(self._h, buf, slots))
+
+    def peer_open_local(self, owner: "GPURenderer5"):
+        self._check(self._L.vr5_peer_open_local(self._h, owner._h))
+
+    def peer_render(self, params: Params, seq: int):
+        self._check(self._L.vr5_peer_render(self._h, C.byref(params), seq))
+
+    def peer_wait(self, seq: int) -> int:
+        p = C.c_void_p()
+        self._check(self._L.vr5_peer_wait(self._h, seq, C.byref(p)))
+        return p.value
+
+    def peer_release(self, seq: int):
+        self._check(self._L.vr5_peer_release(self._h, seq))
+
+    def peer_status(self):
+        self._check(self._L.vr5_peer_status(self._h))
+
+    def peer_close(self):
+        self._L.vr5_peer_close(self._h)
+
     def device_alloc(self, nbytes) -> int:
         p = self._L.vr5_device_alloc(self._h, nbytes)
         if not p:
