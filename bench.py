@@ -264,6 +264,8 @@ def run_b200_arm(args, wl):
     # N > 1: "peer" = every rank's kernel stores its pixels straight into rank 0's frame ring over NVLink (fused render +
     # gather, csrc/vr5_peer.cu); "nccl" = packed strips + dist.gather + unpack kernel (the plain-collective baseline)
     gather = args.gather if world > 1 else "none"
+    lanes = 1 if gather == "nccl" else args.overlap   # the NCCL gather consumes each frame on the one torch stream
+    gpu.set_overlap(lanes)
     gpu.set_partition(rank, world, world > 1 and gather == "nccl")
     PEER_SLOTS = 4
     if gather == "peer":
@@ -276,17 +278,19 @@ def run_b200_arm(args, wl):
 
     L = R.lib()
     rows_padded = max(L.vr5_strip_rows(h, r, world) for r in range(world))
-    frame_dev = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
+    frame_devs = [torch.empty((h, w, 4), dtype=torch.uint8, device=dev) for _ in range(lanes)]  # frames in flight differ
+    frame_dev = frame_devs[0]
     packed = torch.empty((rows_padded, w, 4), dtype=torch.uint8, device=dev) if gather == "nccl" else None
     gathered = torch.empty((world, rows_padded, w, 4), dtype=torch.uint8, device=dev) if (gather == "nccl" and rank == 0) else None
-    pinned = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
-    pinned_np = pinned.numpy() if rank == 0 else None
+    pinneds = [torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() for _ in range(lanes)] if rank == 0 else None
+    pinned = pinneds[0] if rank == 0 else None
 
     def step_device(p):
         """One frame, device resident: N=1 renders in place; N>1 renders this rank's strips, gathers them to rank 0
         over NCCL and scatters them into the frame there. Everything is enqueued on one stream, no host sync."""
         if world == 1:
-            gpu.render_device(p, frame_dev.data_ptr(), blocking=False)
+            gpu.render_device(p, frame_devs[seq[0] % lanes].data_ptr(), blocking=False)
+            seq[0] += 1
         elif gather == "peer":
             gpu.peer_render(p, seq[0])
             if rank == 0:
@@ -300,16 +304,26 @@ def run_b200_arm(args, wl):
                 gpu.unpack_strips(gathered.data_ptr(), rows_padded, world, frame_dev.data_ptr())
 
     def step_e2e(p):
-        """The call a user makes: frame lands in HOST memory (pinned), blocking, like renderers 1-2 of the reference."""
-        if world == 1:
+        """The call a user makes: the frame lands in HOST memory (pinned), like renderers 1-2 of the reference. With one
+        lane the call blocks per frame; with frame overlap frame i is enqueued (kernel + D2H on its lane) and the host
+        then waits for frame i - lanes + 1, i.e. it receives every frame, in order, lanes - 1 frames behind."""
+        i = seq[0]
+        if world == 1 and lanes == 1:
             gpu.render_to_pinned(p, pinned.data_ptr())
-        elif gather == "peer":
-            gpu.peer_render(p, seq[0])
-            if rank == 0:
-                gpu.memcpy_d2h(pinned_np, gpu.peer_wait(seq[0]))   # blocking D2H of the complete frame
-                gpu.peer_release(seq[0])
+        elif world == 1:
+            gpu.render_async_host(p, pinneds[i % lanes].data_ptr())
             seq[0] += 1
-            stream.synchronize()
+            if i >= lanes - 1:
+                gpu.sync_lane((i - (lanes - 1)) % lanes)
+        elif gather == "peer":
+            gpu.peer_render(p, i)
+            if rank == 0:
+                gpu.peer_wait(i)
+                gpu.peer_read(i, pinneds[i % lanes].data_ptr())   # D2H of the complete frame, on the frame's lane
+                gpu.peer_release(i)
+            seq[0] += 1
+            if i >= lanes - 1:
+                gpu.peer_sync_frame(i - (lanes - 1))
         else:
             step_device(p)
             if rank == 0:
@@ -317,6 +331,11 @@ def run_b200_arm(args, wl):
             stream.synchronize()
 
     def barrier():
+        if world == 1:
+            gpu.set_overlap(lanes)   # every lane idle, next vr5_render* call on lane 0 ...
+            seq[0] += (-seq[0]) % lanes   # ... and this script's buffer index with it
+        else:
+            gpu.sync()               # peer frames keep their sequence: lane = seq % lanes, slot = seq % slots on every rank
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
@@ -344,6 +363,7 @@ def run_b200_arm(args, wl):
     e0.record(stream)
     for p in frames:
         step_device(p)
+    gpu.join()           # the stream waits (on the device) for the last frame of every lane
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
@@ -402,7 +422,7 @@ def run_b200_arm(args, wl):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "fps": args.steps / (ms * 1e-3),
             "config": {"workload": wl["name"], "volume": "%d^3" % n, "viewport": "%dx%d" % (w, h), "tf": wl["tf"],
-                       "projection": "orthographic", "sampler": args.sampler, "samples_per_frame": samples_total / args.steps,
+                       "projection": "orthographic", "sampler": args.sampler, "frame_overlap_lanes": lanes, "samples_per_frame": samples_total / args.steps,
                        "parallelism": ("image-space strips x%d, volume replicated, %s" % (world, "pixels stored straight into rank 0's frame ring over NVLink peer memory (fused render + gather)" if gather == "peer" else "NCCL gather to rank 0")) if world > 1 else "single GPU",
                        "l2": "no flush in the timed loop: per frame the kernel reads the %.0f MB volume and writes the %.1f MB frame (L2 is 126 MB); "
                              "the flushed per-kernel time is reported in roofline.kernel_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
@@ -453,6 +473,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--overlap", type=int, default=2, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how strips reach rank 0")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

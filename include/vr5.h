@@ -107,10 +107,22 @@ int vr5_render(vr5_renderer *r, const vr5_params *p, void *out_rgba8, int out_is
 int vr5_render_raycaster(vr5_renderer *r, const vr5_raycaster *rc, void *out_rgba8, int out_is_device);
 /* Non-blocking variant for device buffers (or pinned host buffers): enqueue on the renderer's stream and return. */
 int vr5_render_async(vr5_renderer *r, const vr5_params *p, void *out_rgba8, int out_is_device);
-/* cudaStreamSynchronize on the renderer's stream. */
+/* cudaStreamSynchronize on the renderer's stream and on every frame lane. */
 int vr5_sync(vr5_renderer *r);
 /* Use an external stream (a cudaStream_t passed as void*, e.g. torch's current stream); NULL restores the own stream. */
 int vr5_set_stream(vr5_renderer *r, void *cuda_stream);
+/* Frame overlap. lanes = 1 (default): every frame runs on the renderer's stream, in order - the reference's behaviour.
+ * lanes = 2..4: successive frames (vr5_render*, vr5_peer_render) go round-robin over that many internal streams, so the
+ * tail of one frame's kernel (a few long rays left, most SMs idle) overlaps the start of the next frame, and a host
+ * frame's D2H copy overlaps the next kernel. Each lane is ordered AFTER what the caller enqueued on the renderer's stream
+ * before the call; the renderer's stream waits for the lanes only in vr5_join / vr5_sync (a blocking vr5_render waits for
+ * its own frame). Output buffers of frames in flight must differ. */
+int vr5_set_overlap(vr5_renderer *r, int lanes);
+int vr5_get_overlap(const vr5_renderer *r);
+/* Make the renderer's stream wait (on the device) for every frame launched so far. No-op with one lane. */
+int vr5_join(vr5_renderer *r);
+/* Block the host until lane `lane` is idle. The k-th vr5_render* call since vr5_set_overlap runs on lane k % lanes. */
+int vr5_sync_lane(vr5_renderer *r, int lane);
 
 /* ---- measurement extras (headless bench driver; replace Profiler.cpp:46-78) -------------------------------- */
 
@@ -146,9 +158,10 @@ int vr5_unpack_strips(vr5_renderer *r, const void *packed_all, uint32_t rows_pad
 /* The gathering rank ("owner") holds a ring of `slots` full frames plus flag words in one device allocation; every other
  * rank maps it (CUDA IPC) and its ray-cast kernel stores each pixel straight into its final place in the owner's frame
  * over NVLink. Frames carry a sequence number seq = 0, 1, 2, ... agreed by all ranks; frame seq lives in slot seq % slots.
- * Flags: arrive[slot] counts writer ranks that finished a frame in that slot; consumed = frames released by the owner.
+ * Flags: arrive[slot] counts writer ranks that finished a frame in that slot; consumed[slot] = frames of it released.
  * A writer may store frame seq only after frame seq - slots was released; the owner may read frame seq only after all
- * world - 1 writers arrived. Both conditions are enforced on the device by one-thread wait kernels (bounded: a wait
+ * world - 1 writers arrived. With frame overlap (vr5_set_overlap) frame seq runs on lane seq % lanes - slots must be a
+ * multiple of lanes - and vr5_peer_wait / read / release of a frame are enqueued on that frame's lane. Both conditions are enforced on the device by one-thread wait kernels (bounded: a wait
  * that exceeds the timeout sets a status flag instead of hanging). One process per GPU; never two ranks on one GPU. */
 #define VR5_PEER_HANDLE_BYTES 64
 /* owner: allocate the ring for the current window (vr5_set_window first); slots >= 1 */
@@ -164,8 +177,12 @@ int vr5_peer_render(vr5_renderer *r, const vr5_params *p, uint64_t seq);
 /* owner: enqueue the wait for all writers of frame `seq`; *frame_dev_out = device pointer of the complete frame, valid
  * for work enqueued on the renderer's stream after this call and before vr5_peer_release(seq) */
 int vr5_peer_wait(vr5_renderer *r, uint64_t seq, void **frame_dev_out);
+/* owner: async D2H copy of frame `seq` (after vr5_peer_wait(seq)) into a (pinned) host buffer, on the frame's lane */
+int vr5_peer_read(vr5_renderer *r, uint64_t seq, void *host_dst);
 /* owner: frame `seq` is consumed; its slot may be overwritten by frame seq + slots */
 int vr5_peer_release(vr5_renderer *r, uint64_t seq);
+/* any rank: block the host until everything enqueued for frame `seq` (render, wait, read, release) has finished */
+int vr5_peer_sync_frame(vr5_renderer *r, uint64_t seq);
 /* 0 = ok, 1 = some device-side wait timed out since vr5_peer_create / vr5_peer_open (synchronises the stream) */
 int vr5_peer_status(vr5_renderer *r);
 void vr5_peer_close(vr5_renderer *r);

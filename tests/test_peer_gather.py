@@ -22,7 +22,8 @@ def _scene(R, port, golden, volumes):
 
 
 @pytest.mark.gpu
-def test_ring_protocol_single_gpu(R, port, golden, volumes):
+@pytest.mark.parametrize("lanes", [1, 2])
+def test_ring_protocol_single_gpu(lanes, R, port, golden, volumes):
     case, scene, params = _scene(R, port, golden, volumes)
     w, h = case["width"], case["height"]
     owner, writer = R.GPURenderer5(0), R.GPURenderer5(0)
@@ -31,6 +32,7 @@ def test_ring_protocol_single_gpu(R, port, golden, volumes):
             g.set_window_buffer(w, h)
             g.set_scene(scene)
             g.set_partition(rank, 2, False)
+            g.set_overlap(lanes)
         whole = R.GPURenderer5(0)
         whole.set_window_buffer(w, h)
         whole.set_scene(scene)
@@ -47,7 +49,8 @@ def test_ring_protocol_single_gpu(R, port, golden, volumes):
             ptr = owner.peer_wait(seq)        # satisfied: the writer arrived and was synchronised
             ptrs.add(ptr)
             got = np.zeros((h, w, 4), dtype=np.uint8)
-            owner.memcpy_d2h(got, ptr)
+            owner.peer_read(seq, got.ctypes.data)
+            owner.peer_sync_frame(seq)
             assert np.array_equal(got, want), seq
             owner.peer_release(seq)
             owner.sync()
@@ -91,6 +94,7 @@ def _two_gpu_worker(rank, world, port_no, ret):
         gpu.set_partition(0, 1, False)
         want = [gpu.render_volume(p) for p in frames]
     gpu.set_partition(rank, world, False)
+    gpu.set_overlap(2)
     slots = 2
     box = [gpu.peer_create(slots) if rank == 0 else None]
     dist.broadcast_object_list(box, src=0)
@@ -101,11 +105,12 @@ def _two_gpu_worker(rank, world, port_no, ret):
     for seq, p in enumerate(frames):      # no host synchronisation between ranks inside the loop: the flags do it
         gpu.peer_render(p, seq)
         if rank == 0:
-            ptr = gpu.peer_wait(seq)
+            gpu.peer_wait(seq)
             got = np.zeros((h, w, 4), dtype=np.uint8)
-            gpu.memcpy_d2h(got, ptr)
-            ok = ok and np.array_equal(got, want[seq])
+            gpu.peer_read(seq, got.ctypes.data)
             gpu.peer_release(seq)
+            gpu.peer_sync_frame(seq)
+            ok = ok and np.array_equal(got, want[seq])
     gpu.peer_status()
     gpu.sync()
     dist.barrier()
@@ -133,3 +138,39 @@ def test_two_gpus_ipc():
             p.kill()
             pytest.fail("peer gather worker hung")
     assert dict(ret) == {0: True, 1: True}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("lanes", [2, 3])
+def test_frame_overlap_equals_serial(lanes, R, port, golden, volumes):
+    """vr5_set_overlap: frames in flight on several lanes (own queue counters, own internal framebuffers) give the same
+    bytes as the serial renderer, for device and for host outputs."""
+    case, scene, _ = _scene(R, port, golden, volumes)
+    w, h = case["width"], case["height"]
+    gpu = R.GPURenderer5(0)
+    try:
+        gpu.set_window_buffer(w, h)
+        gpu.set_scene(scene)
+        frames = [scene.params(R.camera(w, h, i % 2, (10.0 * i, 47.0 * i, 0.0), 2.0)) for i in range(7)]
+        want = [gpu.render_volume(p) for p in frames]
+        gpu.set_overlap(lanes)
+        host = [np.zeros((h, w, 4), dtype=np.uint8) for _ in frames]
+        for p, out in zip(frames, host):          # all in flight, distinct outputs
+            gpu.render_async_host(p, out.ctypes.data)
+        gpu.sync()
+        for a, b in zip(host, want):
+            assert np.array_equal(a, b)
+        dev = [gpu.device_alloc(w * h * 4) for _ in frames]
+        for p, d in zip(frames, dev):
+            gpu.render_device(p, d, blocking=False)
+        gpu.join()                                 # the renderer's stream now waits for every lane
+        for d, b in zip(dev, want):
+            got = np.zeros((h, w, 4), dtype=np.uint8)
+            gpu.memcpy_d2h(got, d)                 # enqueued on the renderer's stream
+            assert np.array_equal(got, b)
+            gpu.device_free(d)
+        assert gpu.count(frames[3]) == gpu.count(frames[3])
+        gpu.set_overlap(1)
+        assert np.array_equal(gpu.render_volume(frames[2]), want[2])
+    finally:
+        gpu.close()

@@ -91,6 +91,10 @@ def lib() -> C.CDLL:
         "vr5_render_async": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),
         "vr5_sync": (C.c_int, [vp]),
         "vr5_set_stream": (C.c_int, [vp, vp]),
+        "vr5_set_overlap": (C.c_int, [vp, C.c_int]),
+        "vr5_get_overlap": (C.c_int, [vp]),
+        "vr5_join": (C.c_int, [vp]),
+        "vr5_sync_lane": (C.c_int, [vp, C.c_int]),
         "vr5_render_timed": (C.c_int, [vp, C.POINTER(Params), C.c_int, vp, C.c_int, f32p]),
         "vr5_count": (C.c_int, [vp, C.POINTER(Params), C.POINTER(Counters)]),
         "vr5_launch_count": (C.c_uint64, [vp]),
@@ -109,6 +113,8 @@ def lib() -> C.CDLL:
         "vr5_peer_render": (C.c_int, [vp, C.POINTER(Params), C.c_uint64]),
         "vr5_peer_wait": (C.c_int, [vp, C.c_uint64, C.POINTER(vp)]),
         "vr5_peer_release": (C.c_int, [vp, C.c_uint64]),
+        "vr5_peer_read": (C.c_int, [vp, C.c_uint64, vp]),
+        "vr5_peer_sync_frame": (C.c_int, [vp, C.c_uint64]),
         "vr5_peer_status": (C.c_int, [vp]),
         "vr5_peer_close": (None, [vp]),
         "vr5_synth_volume": (C.c_int, [vp, C.c_int, C.c_uint16, C.c_uint32]),

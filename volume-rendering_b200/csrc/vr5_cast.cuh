@@ -86,7 +86,9 @@ struct KArgs {
     int rank, world;
     // tile queue
     unsigned *queue;         // this frame's counter
-    unsigned *queue_next;    // zeroed by this frame for the next one
+    uint32_t queue_base;     // value of the counter when this launch starts: the counter is never reset. Every launch adds
+                             // exactly n_queue + (number of warps in the grid) to it (each warp ends on one failed fetch),
+                             // so the host knows the next base without touching the device (vr5_render.cu, launch)
     uint32_t n_queue;        // padded tile count
     uint32_t tiles_x, tile_rows_local, groups_x;
     Counters *counters;
@@ -416,7 +418,6 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
     __shared__ Pinned s_pinned;
     for (int i = threadIdx.x; i < 256; i += kCtaThreads) s_lut[i] = a.tf[i >> 1];
     for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
-    if (blockIdx.x == 0 && threadIdx.x == 0) *a.queue_next = 0u;  // arm the other counter for the next frame
     if (threadIdx.x == 0) s_pinned = Pinned{a.hx, a.hy, a.hz, a.step, a.threshold, a.wmx, a.wmy, a.wmz, a.whi, a.wsx, a.wsxy};
     __syncthreads();
 
@@ -430,7 +431,7 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
     Counters cnt = {0, 0, 0, 0, 0};
     for (;;) {
         unsigned q = 0;
-        if (lane == 0) q = atomicAdd(a.queue, 1u);
+        if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
         q = __shfl_sync(0xffffffffu, q, 0);
         if (q >= a.n_queue) break;
         const uint32_t group = q >> (kGroupLog2X + kGroupLog2Y), within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);

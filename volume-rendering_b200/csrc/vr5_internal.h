@@ -15,7 +15,6 @@ struct vr5_renderer {
     // window
     uint16_t width = 0, height = 0;
     size_t frame_bytes = 0;
-    uint8_t *d_frame = nullptr;  // internal framebuffer used when the caller hands a host pointer
     // tables
     float *d_tf = nullptr;        // 128 x float4, pre-multiplied
     uint32_t *d_esl = nullptr;    // 1024 words
@@ -43,9 +42,22 @@ struct vr5_renderer {
     uint32_t bxn = 0, byn = 0, bzn = 0;
     cudaArray_t d_array = nullptr;
     cudaTextureObject_t tex = 0;
-    // tile queue: two counters used alternately; each frame's kernel re-arms the other one
-    unsigned *d_queue = nullptr;
-    int parity = 0;
+    // frame lanes (vr5_set_overlap): frames go round-robin over n_lanes streams so that the tail of one frame's kernel
+    // (few long rays left) overlaps the start of the next. Each lane owns a tile-queue counter (monotonic, see
+    // KArgs::queue_base) and an internal framebuffer for host outputs. With one lane, lane 0 runs on `stream`.
+    struct Lane {
+        cudaStream_t stream = nullptr;
+        unsigned *d_queue = nullptr;
+        uint32_t queue_base = 0;
+        cudaEvent_t done = nullptr;
+        bool pending = false;        // a frame was launched on this lane and `stream` has not been made to wait for it
+        uint8_t *d_frame = nullptr;
+    } lanes[4];
+    int n_lanes = 1;
+    uint64_t frame_no = 0;
+    cudaEvent_t ev_fork = nullptr;
+    cudaStream_t launch_stream = nullptr;  // set by launch() for launch_one()
+    uint32_t last_grid = 0;
     void *d_counters = nullptr;
     // partition
     int rank = 0, world = 1, packed = 0;
@@ -54,7 +66,7 @@ struct vr5_renderer {
     bool peer_owner = false, peer_ipc_mapped = false;
     int peer_slots = 0;
     size_t peer_frame_stride = 0;
-    uint64_t peer_released = 0;       // owner, host side: frames released so far
+    uint32_t peer_released_slot[16] = {0};  // owner, host side: releases per slot so far
     // bookkeeping
     int ctas_per_sm[256] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
@@ -64,7 +76,11 @@ struct vr5_renderer {
 };
 
 void vr5_fail(vr5_renderer *r, const char *what, cudaError_t e, const char *file, int line);
-int vr5_render_into(vr5_renderer *r, const struct vr5_params *p, void *out_dev);  // async launch of the cast kernel, device buffer
+// lane plumbing for vr5_peer.cu: stream of a lane, fork from the user stream before work on a lane, mark its end
+cudaStream_t vr5_lane_stream(vr5_renderer *r, int lane);
+int vr5_lane_begin(vr5_renderer *r, int lane);
+int vr5_lane_end(vr5_renderer *r, int lane);
+int vr5_render_into(vr5_renderer *r, const struct vr5_params *p, void *out_dev, int lane);  // async launch of the cast kernel, device buffer
 int vr5_adopt_volume(vr5_renderer *r, uint8_t *dev_owned, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz);
 
 #define VR5_CUDA(r, call)                                         \

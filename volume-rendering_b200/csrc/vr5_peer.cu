@@ -11,14 +11,16 @@
 
 namespace {
 
-constexpr size_t kHeaderBytes = 4096;          // flag words, one 128-byte line each
+constexpr size_t kHeaderBytes = 8192;          // flag words, one 128-byte line each
 constexpr int kMaxSlots = 16;
 constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;  // a wait that lasts 4 s gives up and raises the status flag
 
-// header layout (uint32 words): [0] consumed, [32] timed_out, [64 + 32 * slot] arrive[slot]
-__host__ __device__ inline uint32_t *consumed_word(uint8_t *base) { return reinterpret_cast<uint32_t *>(base); }
+// header layout (uint32 words, one 128-byte line per flag): [32] timed_out, [64 + 64 * slot] arrive[slot] = writer ranks that
+// finished a frame in that slot (all uses), [96 + 64 * slot] consumed[slot] = uses of that slot the owner has released.
+// Per-slot counters keep the protocol independent of the order in which frames on different lanes complete.
 __host__ __device__ inline uint32_t *timeout_word(uint8_t *base) { return reinterpret_cast<uint32_t *>(base) + 32; }
-__host__ __device__ inline uint32_t *arrive_word(uint8_t *base, int slot) { return reinterpret_cast<uint32_t *>(base) + 64 + 32 * slot; }
+__host__ __device__ inline uint32_t *arrive_word(uint8_t *base, int slot) { return reinterpret_cast<uint32_t *>(base) + 64 + 64 * slot; }
+__host__ __device__ inline uint32_t *consumed_word(uint8_t *base, int slot) { return reinterpret_cast<uint32_t *>(base) + 96 + 64 * slot; }
 
 __device__ __forceinline__ uint32_t load_acquire_sys(const uint32_t *p) {
     uint32_t v;
@@ -61,10 +63,10 @@ uint8_t *slot_ptr(const vr5_renderer *r, uint64_t seq) { return r->peer_base + k
 extern "C" void vr5_peer_close(vr5_renderer *r) {
     if (!r || !r->peer_base) return;
     cudaSetDevice(r->device);
-    cudaStreamSynchronize(r->stream);
+    vr5_sync(r);
     if (r->peer_owner) cudaFree(r->peer_base);
     else if (r->peer_ipc_mapped) cudaIpcCloseMemHandle(r->peer_base);
-    r->peer_base = nullptr; r->peer_owner = false; r->peer_ipc_mapped = false; r->peer_slots = 0; r->peer_released = 0;
+    r->peer_base = nullptr; r->peer_owner = false; r->peer_ipc_mapped = false; r->peer_slots = 0; memset(r->peer_released_slot, 0, sizeof(r->peer_released_slot));
 }
 
 extern "C" int vr5_peer_create(vr5_renderer *r, int slots) {
@@ -78,7 +80,7 @@ extern "C" int vr5_peer_create(vr5_renderer *r, int slots) {
     if (e != cudaSuccess) { r->peer_base = nullptr; vr5_fail(r, "cudaMalloc peer ring", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
     VR5_CUDA(r, cudaMemsetAsync(r->peer_base, 0, bytes, r->stream));
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
-    r->peer_owner = true; r->peer_slots = slots; r->peer_released = 0;
+    r->peer_owner = true; r->peer_slots = slots; memset(r->peer_released_slot, 0, sizeof(r->peer_released_slot));
     return 0;
 }
 
@@ -122,27 +124,36 @@ extern "C" int vr5_peer_open_local(vr5_renderer *r, vr5_renderer *owner) {
     return 0;
 }
 
+// frames of the ring use lane seq % n_lanes; with slots a multiple of the lane count a slot is always reused on the lane
+// that released it, so the owner's own stores need no extra ordering
+static int lane_of(const vr5_renderer *r, uint64_t seq) { return (int)(seq % (uint64_t)r->n_lanes); }
+
 extern "C" int vr5_peer_render(vr5_renderer *r, const vr5_params *p, uint64_t seq) {
     if (!r) return 1;
     if (!r->peer_base) { vr5_fail(r, "vr5_peer_render: no ring (vr5_peer_create / vr5_peer_open)", cudaSuccess, __FILE__, __LINE__); return 1; }
     if (r->packed) { vr5_fail(r, "vr5_peer_render: the partition must be unpacked (pixels go to their final place)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (r->peer_slots % r->n_lanes) { vr5_fail(r, "vr5_peer_render: slots must be a multiple of the overlap lanes", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     const uint64_t slots = (uint64_t)r->peer_slots;
+    const int slot = (int)(seq % slots), lane = lane_of(r, seq);
+    const uint32_t use = (uint32_t)(seq / slots);  // how many frames used this slot before
+    cudaStream_t st = vr5_lane_stream(r, lane);
+    if (vr5_lane_begin(r, lane)) return 1;
     if (r->peer_owner) {
-        // stream order does the rest: vr5_peer_release(seq - slots) was enqueued before this frame's kernel
-        if (seq >= slots && r->peer_released < seq - slots + 1) { vr5_fail(r, "vr5_peer_render: slot not released yet (call vr5_peer_release in frame order)", cudaSuccess, __FILE__, __LINE__); return 1; }
-    } else if (seq >= slots) {
+        // stream order does the rest: vr5_peer_release of the slot's previous frame was enqueued on this lane
+        if (r->peer_released_slot[slot] < use) { vr5_fail(r, "vr5_peer_render: slot not released yet (vr5_peer_release every frame)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    } else if (use > 0) {
         // wait until the owner has released the frame that last used this slot
-        peer_wait_kernel<<<1, 1, 0, r->stream>>>(consumed_word(r->peer_base), (uint32_t)(seq - slots + 1), timeout_word(r->peer_base));
+        peer_wait_kernel<<<1, 1, 0, st>>>(consumed_word(r->peer_base, slot), use, timeout_word(r->peer_base));
         r->launches++;
     }
-    if (vr5_render_into(r, p, slot_ptr(r, seq))) return 1;
+    if (vr5_render_into(r, p, slot_ptr(r, seq), lane)) return 1;
     if (!r->peer_owner) {
-        peer_arrive_kernel<<<1, 1, 0, r->stream>>>(arrive_word(r->peer_base, (int)(seq % slots)));
+        peer_arrive_kernel<<<1, 1, 0, st>>>(arrive_word(r->peer_base, slot));
         r->launches++;
     }
     VR5_CUDA(r, cudaGetLastError());
-    return 0;
+    return vr5_lane_end(r, lane);
 }
 
 extern "C" int vr5_peer_wait(vr5_renderer *r, uint64_t seq, void **frame_dev_out) {
@@ -153,23 +164,40 @@ extern "C" int vr5_peer_wait(vr5_renderer *r, uint64_t seq, void **frame_dev_out
     if (r->world > 1) {
         // every use of a slot adds world - 1 arrivals to its counter
         const uint32_t target = (uint32_t)((seq / slots + 1) * (uint64_t)(r->world - 1));
-        peer_wait_kernel<<<1, 1, 0, r->stream>>>(arrive_word(r->peer_base, (int)(seq % slots)), target, timeout_word(r->peer_base));
+        peer_wait_kernel<<<1, 1, 0, vr5_lane_stream(r, lane_of(r, seq))>>>(arrive_word(r->peer_base, (int)(seq % slots)), target, timeout_word(r->peer_base));
         r->launches++;
         VR5_CUDA(r, cudaGetLastError());
     }
     if (frame_dev_out) *frame_dev_out = slot_ptr(r, seq);
-    return 0;
+    return vr5_lane_end(r, lane_of(r, seq));
+}
+
+extern "C" int vr5_peer_read(vr5_renderer *r, uint64_t seq, void *host_dst) {
+    if (!r) return 1;
+    if (!r->peer_owner || !host_dst) { vr5_fail(r, "vr5_peer_read: owner only, host buffer needed", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaMemcpyAsync(host_dst, slot_ptr(r, seq), r->frame_bytes, cudaMemcpyDeviceToHost, vr5_lane_stream(r, lane_of(r, seq))));
+    return vr5_lane_end(r, lane_of(r, seq));
 }
 
 extern "C" int vr5_peer_release(vr5_renderer *r, uint64_t seq) {
     if (!r) return 1;
     if (!r->peer_owner) { vr5_fail(r, "vr5_peer_release: only the owner releases frames", cudaSuccess, __FILE__, __LINE__); return 1; }
-    if (seq != r->peer_released) { vr5_fail(r, "vr5_peer_release: frames are released in order", cudaSuccess, __FILE__, __LINE__); return 1; }
+    const uint64_t slots = (uint64_t)r->peer_slots;
+    const int slot = (int)(seq % slots);
+    if ((uint32_t)(seq / slots) != r->peer_released_slot[slot]) { vr5_fail(r, "vr5_peer_release: every frame of a slot is released once, in order", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
-    peer_release_kernel<<<1, 1, 0, r->stream>>>(consumed_word(r->peer_base), (uint32_t)(seq + 1));
+    peer_release_kernel<<<1, 1, 0, vr5_lane_stream(r, lane_of(r, seq))>>>(consumed_word(r->peer_base, slot), (uint32_t)(seq / slots + 1));
     r->launches++;
     VR5_CUDA(r, cudaGetLastError());
-    r->peer_released = seq + 1;
+    r->peer_released_slot[slot]++;
+    return vr5_lane_end(r, lane_of(r, seq));
+}
+
+extern "C" int vr5_peer_sync_frame(vr5_renderer *r, uint64_t seq) {
+    if (!r) return 1;
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaStreamSynchronize(vr5_lane_stream(r, lane_of(r, seq))));
     return 0;
 }
 
@@ -178,6 +206,7 @@ extern "C" int vr5_peer_status(vr5_renderer *r) {
     if (!r->peer_base) { vr5_fail(r, "vr5_peer_status: no ring", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     uint32_t flag = 0;
+    if (vr5_sync(r)) return 1;
     VR5_CUDA(r, cudaMemcpyAsync(&flag, timeout_word(r->peer_base), sizeof(flag), cudaMemcpyDeviceToHost, r->stream));
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     if (flag) { vr5_fail(r, "peer ring: a device-side wait timed out (a rank is missing or out of frame order)", cudaSuccess, __FILE__, __LINE__); return 1; }

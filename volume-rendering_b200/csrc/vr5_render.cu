@@ -102,6 +102,71 @@ __global__ void l2_flush_kernel(uint32_t *buf, uint64_t n_words, uint32_t v) {
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (uint64_t)gridDim.x * blockDim.x) buf[i] = v;
 }
 
+// ---- frame lanes ---------------------------------------------------------------------------------------------------
+cudaStream_t vr5_lane_stream(vr5_renderer *r, int lane) { return r->n_lanes == 1 ? r->stream : r->lanes[lane].stream; }
+
+// everything this handle has in flight, on the user stream and on every lane
+static cudaError_t sync_all(vr5_renderer *r) {
+    cudaError_t first = r->stream ? cudaStreamSynchronize(r->stream) : cudaSuccess;
+    for (auto &ln : r->lanes) {
+        if (!ln.stream) continue;
+        const cudaError_t e = cudaStreamSynchronize(ln.stream);
+        if (first == cudaSuccess) first = e;
+        ln.pending = false;
+    }
+    return first;
+}
+
+// Work about to be enqueued on a lane is ordered after whatever the caller has put on the user stream so far (its own
+// consumer of an earlier frame, uploads). The join in the other direction is deferred (vr5_join / vr5_sync / a blocking
+// call): waiting on the user stream right away would chain every frame behind the previous one again.
+int vr5_lane_begin(vr5_renderer *r, int lane) {
+    if (r->n_lanes == 1) return 0;
+    VR5_CUDA(r, cudaEventRecord(r->ev_fork, r->stream));
+    VR5_CUDA(r, cudaStreamWaitEvent(r->lanes[lane].stream, r->ev_fork, 0));
+    return 0;
+}
+
+int vr5_lane_end(vr5_renderer *r, int lane) {
+    if (r->n_lanes == 1) return 0;
+    VR5_CUDA(r, cudaEventRecord(r->lanes[lane].done, r->lanes[lane].stream));
+    r->lanes[lane].pending = true;
+    return 0;
+}
+
+static int ensure_lane_frames(vr5_renderer *r) {
+    for (int i = 0; i < r->n_lanes; i++)
+        if (!r->lanes[i].d_frame && r->frame_bytes) VR5_CUDA(r, cudaMalloc(&r->lanes[i].d_frame, r->frame_bytes));
+    return 0;
+}
+
+extern "C" int vr5_set_overlap(vr5_renderer *r, int lanes) {
+    if (!r) return 1;
+    if (lanes < 1 || lanes > 4) { vr5_fail(r, "vr5_set_overlap: 1..4 lanes", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, sync_all(r));
+    r->n_lanes = lanes;
+    r->frame_no = 0;
+    return ensure_lane_frames(r);
+}
+extern "C" int vr5_get_overlap(const vr5_renderer *r) { return r ? r->n_lanes : -1; }
+
+extern "C" int vr5_join(vr5_renderer *r) {
+    if (!r) return 1;
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    for (int i = 0; i < r->n_lanes && r->n_lanes > 1; i++)
+        if (r->lanes[i].pending) { VR5_CUDA(r, cudaStreamWaitEvent(r->stream, r->lanes[i].done, 0)); r->lanes[i].pending = false; }
+    return 0;
+}
+
+extern "C" int vr5_sync_lane(vr5_renderer *r, int lane) {
+    if (!r) return 1;
+    if (lane < 0 || lane >= r->n_lanes) { vr5_fail(r, "vr5_sync_lane: no such lane", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, cudaStreamSynchronize(vr5_lane_stream(r, lane)));
+    return 0;
+}
+
 // ---- lifecycle ---------------------------------------------------------------------------------------------------
 extern "C" int vr5_version(void) { return VR5_VERSION; }
 extern "C" const char *vr5_name(void) { return "CUDA B200 persistent tile queue (GPURenderer5)"; }
@@ -130,8 +195,13 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     r->stream = r->own_stream;
     if ((e = cudaMalloc(&r->d_tf, VR5_TF_SIZE * sizeof(float4))) != cudaSuccess) return bail("cudaMalloc tf", e);
     if ((e = cudaMalloc(&r->d_esl, VR5_ESL_VOLUME_SIZE * sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc esl", e);
-    if ((e = cudaMalloc(&r->d_queue, 2 * sizeof(unsigned))) != cudaSuccess) return bail("cudaMalloc queue", e);
-    if ((e = cudaMemset(r->d_queue, 0, 2 * sizeof(unsigned))) != cudaSuccess) return bail("cudaMemset queue", e);
+    for (auto &ln : r->lanes) {  // four lanes' worth of streams, counters and events; vr5_set_overlap picks how many are used
+        if ((e = cudaStreamCreateWithFlags(&ln.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate lane", e);
+        if ((e = cudaMalloc(&ln.d_queue, 128)) != cudaSuccess) return bail("cudaMalloc queue", e);
+        if ((e = cudaMemset(ln.d_queue, 0, 128)) != cudaSuccess) return bail("cudaMemset queue", e);
+        if ((e = cudaEventCreateWithFlags(&ln.done, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    }
+    if ((e = cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaMalloc(&r->d_counters, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc counters", e);
     const char *env = getenv("VR5_SAMPLER");
     r->sampler = VR5_SAMPLER_HYBRID_WINDOW;  // fastest path on B200 (profiles/r01_sampler_choice.md); $VR5_SAMPLER overrides
@@ -204,16 +274,21 @@ static void free_layouts(vr5_renderer *r) {
 extern "C" void vr5_destroy(vr5_renderer *r) {
     if (!r) return;
     cudaSetDevice(r->device);
-    if (r->own_stream) cudaStreamSynchronize(r->own_stream);
+    sync_all(r);
+    vr5_peer_close(r);
     free_layouts(r);
     cudaFree(r->d_vol_linear);
-    cudaFree(r->d_frame);
+    for (auto &ln : r->lanes) {
+        cudaFree(ln.d_frame);
+        cudaFree(ln.d_queue);
+        if (ln.done) cudaEventDestroy(ln.done);
+        if (ln.stream) cudaStreamDestroy(ln.stream);
+    }
+    if (r->ev_fork) cudaEventDestroy(r->ev_fork);
     cudaFree(r->d_tf);
     cudaFree(r->d_esl);
-    cudaFree(r->d_queue);
     cudaFree(r->d_counters);
     cudaFree(r->d_flush);
-    vr5_peer_close(r);
     if (r->own_stream) cudaStreamDestroy(r->own_stream);
     delete r;
 }
@@ -223,18 +298,18 @@ extern "C" int vr5_set_window(vr5_renderer *r, uint16_t width, uint16_t height) 
     if (!r) return 1;
     VR5_CUDA(r, cudaSetDevice(r->device));
     if (width == 0 || height == 0) { vr5_fail(r, "vr5_set_window: empty viewport", cudaSuccess, __FILE__, __LINE__); return 1; }
-    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
-    if (r->d_frame) { cudaFree(r->d_frame); r->d_frame = nullptr; }
+    VR5_CUDA(r, sync_all(r));
+    for (auto &ln : r->lanes) if (ln.d_frame) { cudaFree(ln.d_frame); ln.d_frame = nullptr; }
     r->width = width; r->height = height;
     r->frame_bytes = (size_t)width * height * 4;
-    VR5_CUDA(r, cudaMalloc(&r->d_frame, r->frame_bytes));
-    return 0;
+    return ensure_lane_frames(r);
 }
 
 extern "C" int vr5_set_transfer_fn(vr5_renderer *r, const float *tf, const uint32_t *esl_bits) {
     if (!r) return 1;
     if (!tf || !esl_bits) { vr5_fail(r, "vr5_set_transfer_fn: NULL table", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, sync_all(r));
     VR5_CUDA(r, cudaMemcpyAsync(r->d_tf, tf, VR5_TF_SIZE * sizeof(float4), cudaMemcpyHostToDevice, r->stream));
     VR5_CUDA(r, cudaMemcpyAsync(r->d_esl, esl_bits, VR5_ESL_VOLUME_SIZE * sizeof(uint32_t), cudaMemcpyHostToDevice, r->stream));
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
@@ -450,7 +525,7 @@ static int build_layout(vr5_renderer *r) {
 
 static int install_volume(vr5_renderer *r, const uint8_t *src, cudaMemcpyKind kind, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz) {
     VR5_CUDA(r, cudaSetDevice(r->device));
-    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    VR5_CUDA(r, sync_all(r));
     free_layouts(r);
     if (r->d_vol_linear) { cudaFree(r->d_vol_linear); r->d_vol_linear = nullptr; }
     r->vol_bytes = 0;
@@ -484,7 +559,7 @@ extern "C" int vr5_set_volume_device(vr5_renderer *r, const uint8_t *dev, uint64
 
 // adopt a linear device buffer allocated by this library (device generator) without copying
 int vr5_adopt_volume(vr5_renderer *r, uint8_t *dev_owned, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz) {
-    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    VR5_CUDA(r, sync_all(r));
     free_layouts(r);
     if (r->d_vol_linear) cudaFree(r->d_vol_linear);
     r->d_vol_linear = dev_owned; r->vol_bytes = bytes; r->nx = dx; r->ny = dy; r->nz = dz;
@@ -504,7 +579,7 @@ extern "C" int vr5_set_sampler(vr5_renderer *r, int sampler) {
     if (!r) return 1;
     if (sampler < 0 || sampler > VR5_SAMPLER_HYBRID_WINDOW2) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
-    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    VR5_CUDA(r, sync_all(r));
     if (sampler == r->sampler && (r->d_vol_padded || r->d_vol_brick || r->tex || r->d_vol_window || r->p2_wl || !r->d_vol_linear)) return 0;
     r->sampler = sampler;
     return build_layout(r);
@@ -541,7 +616,8 @@ static cudaError_t launch_one(vr5_renderer *r, const KArgs &a) {
     uint32_t grid = (uint32_t)(r->num_sms * per_sm);  // persistent: every CTA resident, a multiple of the SM count
     const uint32_t needed = (a.n_queue + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
     if (grid > needed) grid = needed ? needed : 1;
-    cast_kernel<S, C, SH, CL><<<grid, kCtaThreads, 0, r->stream>>>(a);
+    cast_kernel<S, C, SH, CL><<<grid, kCtaThreads, 0, r->launch_stream>>>(a);
+    r->last_grid = grid;
     r->launches++;
     r->last_variant = S;
     return cudaGetLastError();
@@ -599,8 +675,6 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
     const uint32_t groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
     a->n_queue = (a->groups_x * groups_y) << (kGroupLog2X + kGroupLog2Y);
-    a->queue = r->d_queue + r->parity;
-    a->queue_next = r->d_queue + (r->parity ^ 1);
     a->counters = reinterpret_cast<Counters *>(r->d_counters);
     return 0;
 }
@@ -648,7 +722,21 @@ static cudaError_t launch_p2(vr5_renderer *r, const KArgs &a, bool shade, int mo
     return cudaErrorInvalidValue;
 }
 
-static int launch(vr5_renderer *r, KArgs a, bool count) {
+static int launch_variant(vr5_renderer *r, KArgs &a, bool count);
+
+// one cast-kernel launch on a lane: hand it the lane's queue counter and account for what the launch adds to it
+static int launch(vr5_renderer *r, KArgs a, bool count, int lane) {
+    vr5_renderer::Lane &ln = r->lanes[lane];
+    a.queue = ln.d_queue;
+    a.queue_base = ln.queue_base;
+    r->launch_stream = vr5_lane_stream(r, lane);
+    r->last_grid = 0;
+    const int rc = launch_variant(r, a, count);
+    if (r->last_grid) ln.queue_base += a.n_queue + r->last_grid * (uint32_t)(kCtaThreads / 32);  // last_grid == 0: nothing was launched
+    return rc;
+}
+
+static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
     // shading can only trigger when light_kd > 0.01 (folded into shade_alpha) and some TF entry has alpha > 0.05
     const bool shade = r->tf_can_shade && a.shade_alpha < std::numeric_limits<float>::infinity();
     // the padded texture may be indexed without the upper clamp when rays are clipped to the cube it covers
@@ -660,7 +748,6 @@ static int launch(vr5_renderer *r, KArgs a, bool count) {
     if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW && r->p2_wl && !count && cube && window_ok(r, a)) {
         a.whi = r->p2_hi; a.wmx = r->p2_mx; a.wmy = r->p2_my; a.wmz = r->p2_mz; a.tex_p2 = r->tex_p2; a.wsx = r->p2_sx; a.wsxy = r->p2_sxy;
         e = launch_p2(r, a, shade, r->sampler - VR5_SAMPLER_HYBRID_WINDOW);
-        r->parity ^= 1;
         if (e != cudaSuccess) { vr5_fail(r, "cast_kernel launch", e, __FILE__, __LINE__); return 1; }
         return 0;
     }
@@ -673,7 +760,6 @@ static int launch(vr5_renderer *r, KArgs a, bool count) {
         case VR5_SAMPLER_HYBRID_WINDOW2: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<6, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         default: e = cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
     }
-    r->parity ^= 1;
     if (e != cudaSuccess) { vr5_fail(r, "cast_kernel launch", e, __FILE__, __LINE__); return 1; }
     return 0;
 }
@@ -692,22 +778,27 @@ static int render_impl(vr5_renderer *r, const vr5_params *p, void *out, int out_
     if (!out) { vr5_fail(r, "vr5_render: NULL buffer", cudaSuccess, __FILE__, __LINE__); return 1; }  // GPURenderer1.cu:101
     VR5_CUDA(r, cudaSetDevice(r->device));
     const int is_dev = resolve_is_device(r, out, out_is_device);
-    if (!is_dev && !r->d_frame) { vr5_fail(r, "vr5_render: vr5_set_window not called", cudaSuccess, __FILE__, __LINE__); return 1; }
+    const int lane = (int)(r->frame_no++ % (uint64_t)r->n_lanes);
+    vr5_renderer::Lane &ln = r->lanes[lane];
+    if (!is_dev && !ln.d_frame) { vr5_fail(r, "vr5_render: vr5_set_window not called", cudaSuccess, __FILE__, __LINE__); return 1; }
     KArgs a;
-    if (fill_args(r, p, is_dev ? out : (void *)r->d_frame, &a)) return 1;
-    if (launch(r, a, false)) return 1;
-    if (!is_dev) {
+    if (fill_args(r, p, is_dev ? out : (void *)ln.d_frame, &a)) return 1;
+    if (vr5_lane_begin(r, lane)) return 1;
+    if (launch(r, a, false, lane)) return 1;
+    cudaStream_t st = vr5_lane_stream(r, lane);
+    if (!is_dev) {  // the copy rides on the frame's lane: with two lanes it overlaps the next frame's kernel
         const size_t rows = r->packed ? vr5_strip_rows(r->height, r->rank, r->world) : r->height;
-        VR5_CUDA(r, cudaMemcpyAsync(out, r->d_frame, rows * r->width * 4, cudaMemcpyDeviceToHost, r->stream));
+        VR5_CUDA(r, cudaMemcpyAsync(out, ln.d_frame, rows * r->width * 4, cudaMemcpyDeviceToHost, st));
     }
-    if (blocking) VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    if (vr5_lane_end(r, lane)) return 1;
+    if (blocking) { VR5_CUDA(r, cudaStreamSynchronize(st)); ln.pending = false; }
     return 0;
 }
 
-int vr5_render_into(vr5_renderer *r, const vr5_params *p, void *out_dev) {
+int vr5_render_into(vr5_renderer *r, const vr5_params *p, void *out_dev, int lane) {
     KArgs a;
     if (fill_args(r, p, out_dev, &a)) return 1;
-    return launch(r, a, false);
+    return launch(r, a, false, lane);
 }
 
 extern "C" int vr5_render(vr5_renderer *r, const vr5_params *p, void *out, int out_is_device) { return render_impl(r, p, out, out_is_device, true); }
@@ -728,14 +819,14 @@ extern "C" int vr5_render_raycaster(vr5_renderer *r, const vr5_raycaster *rc, vo
 extern "C" int vr5_sync(vr5_renderer *r) {
     if (!r) return 1;
     VR5_CUDA(r, cudaSetDevice(r->device));
-    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    VR5_CUDA(r, sync_all(r));
     return 0;
 }
 
 extern "C" int vr5_set_stream(vr5_renderer *r, void *cuda_stream) {
     if (!r) return 1;
     VR5_CUDA(r, cudaSetDevice(r->device));
-    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    VR5_CUDA(r, sync_all(r));
     if (cuda_stream) { r->stream = (cudaStream_t)cuda_stream; r->external_stream = true; }
     else { r->stream = r->own_stream; r->external_stream = false; }
     return 0;
@@ -746,6 +837,8 @@ extern "C" int vr5_render_timed(vr5_renderer *r, const vr5_params *frames, int n
     if (!r) return 1;
     if (!frames || n_frames <= 0 || !out_dev || !ms_out) { vr5_fail(r, "vr5_render_timed: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, sync_all(r));
+    cudaStream_t st = vr5_lane_stream(r, 0);  // serial on lane 0: per-launch times must not overlap
     if (l2_flush && !r->d_flush) {
         r->flush_bytes = r->l2_bytes * 2 > (256u << 20) ? r->l2_bytes * 2 : (256u << 20);
         VR5_CUDA(r, cudaMalloc(&r->d_flush, r->flush_bytes));
@@ -755,16 +848,16 @@ extern "C" int vr5_render_timed(vr5_renderer *r, const vr5_params *frames, int n
     int rc = 0;
     for (int f = 0; f < n_frames && !rc; f++) {
         if (l2_flush) {
-            l2_flush_kernel<<<r->num_sms * 4, 512, 0, r->stream>>>(reinterpret_cast<uint32_t *>(r->d_flush), r->flush_bytes / 4, (uint32_t)f);
+            l2_flush_kernel<<<r->num_sms * 4, 512, 0, st>>>(reinterpret_cast<uint32_t *>(r->d_flush), r->flush_bytes / 4, (uint32_t)f);
             r->launches++;
         }
         KArgs a;
         if (fill_args(r, frames + f, out_dev, &a)) { rc = 1; break; }
-        cudaEventRecord(ev[2 * f], r->stream);
-        rc = launch(r, a, false);
-        cudaEventRecord(ev[2 * f + 1], r->stream);
+        cudaEventRecord(ev[2 * f], st);
+        rc = launch(r, a, false, 0);
+        cudaEventRecord(ev[2 * f + 1], st);
     }
-    cudaError_t e = cudaStreamSynchronize(r->stream);
+    cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) { vr5_fail(r, "vr5_render_timed sync", e, __FILE__, __LINE__); rc = 1; }
     if (!rc)
         for (int f = 0; f < n_frames; f++) cudaEventElapsedTime(ms_out + f, ev[2 * f], ev[2 * f + 1]);
@@ -778,11 +871,13 @@ extern "C" int vr5_count(vr5_renderer *r, const vr5_params *p, vr5_counters *out
     VR5_CUDA(r, cudaSetDevice(r->device));
     KArgs a;
     if (fill_args(r, p, nullptr, &a)) return 1;
-    VR5_CUDA(r, cudaMemsetAsync(r->d_counters, 0, sizeof(Counters), r->stream));
-    if (launch(r, a, true)) return 1;
+    VR5_CUDA(r, sync_all(r));
+    cudaStream_t st = vr5_lane_stream(r, 0);
+    VR5_CUDA(r, cudaMemsetAsync(r->d_counters, 0, sizeof(Counters), st));
+    if (launch(r, a, true, 0)) return 1;
     static_assert(sizeof(Counters) == sizeof(vr5_counters), "counter layout");
-    VR5_CUDA(r, cudaMemcpyAsync(out, r->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, r->stream));
-    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    VR5_CUDA(r, cudaMemcpyAsync(out, r->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    VR5_CUDA(r, cudaStreamSynchronize(st));
     return 0;
 }
 

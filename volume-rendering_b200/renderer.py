@@ -199,6 +199,20 @@ class GPURenderer5:
     def set_stream(self, stream_ptr):
         self._check(self._L.vr5_set_stream(self._h, stream_ptr))
 
+    def set_overlap(self, lanes: int):
+        """Frames round-robin over `lanes` internal streams (vr5_set_overlap)."""
+        self._check(self._L.vr5_set_overlap(self._h, lanes))
+
+    def join(self):
+        self._check(self._L.vr5_join(self._h))
+
+    def sync_lane(self, lane: int):
+        self._check(self._L.vr5_sync_lane(self._h, lane))
+
+    def render_async_host(self, params: Params, host_ptr: int):
+        """Non-blocking frame into a pinned host buffer (kernel + D2H on the frame's lane)."""
+        self._check(self._L.vr5_render_async(self._h, C.byref(params), host_ptr, 0))
+
     def set_partition(self, rank, world, packed):
         self._check(self._L.vr5_set_partition(self._h, rank, world, 1 if packed else 0))
 
@@ -227,6 +241,12 @@ class GPURenderer5:
         p = C.c_void_p()
         self._check(self._L.vr5_peer_wait(self._h, seq, C.byref(p)))
         return p.value
+
+    def peer_read(self, seq: int, host_ptr: int):
+        self._check(self._L.vr5_peer_read(self._h, seq, host_ptr))
+
+    def peer_sync_frame(self, seq: int):
+        self._check(self._L.vr5_peer_sync_frame(self._h, seq))
 
     def peer_release(self, seq: int):
         self._check(self._L.vr5_peer_release(self._h, seq))
