@@ -267,7 +267,7 @@ def run_b200_arm(args, wl):
     lanes = 1 if gather == "nccl" else args.overlap   # the NCCL gather consumes each frame on the one torch stream
     gpu.set_overlap(lanes)
     gpu.set_partition(rank, world, world > 1 and gather == "nccl")
-    PEER_SLOTS = 4
+    PEER_SLOTS = 2 * max(1, args.overlap)   # a multiple of the lanes; two uses of headroom per lane
     if gather == "peer":
         box = [gpu.peer_create(PEER_SLOTS) if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)
@@ -473,7 +473,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--overlap", type=int, default=2, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
+    ap.add_argument("--overlap", type=int, default=4, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how strips reach rank 0")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
