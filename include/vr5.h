@@ -51,7 +51,7 @@ typedef struct vr5_counters {
     uint64_t shaded;     /* samples that took the shading path (second voxel fetch) */
 } vr5_counters;
 
-/* Voxel sampler policies (all nearest-neighbour, bit-identical results; they differ in memory path only). */
+/* Voxel sampler policies. 0..6 are nearest-neighbour with bit-identical results (they differ in memory path only). */
 enum { VR5_SAMPLER_LINEAR = 0,  /* x-fastest linear array, LDG.U8 (the reference's layout, ModelBase.h:18-22) */
        VR5_SAMPLER_BRICK = 1,   /* 8x4x4-voxel bricks (one 128-B line each, 4x4x2 per 32-B sector), LDG.U8 */
        VR5_SAMPLER_TEX3D = 2,   /* cudaArray 3-D texture, integer-coordinate point fetch (TLD) */
@@ -59,7 +59,11 @@ enum { VR5_SAMPLER_LINEAR = 0,  /* x-fastest linear array, LDG.U8 (the reference
        VR5_SAMPLER_HYBRID_WINDOW = 4,  /* texture : window layout 1 : 1. Window = doubly padded linear array inside one 4-GiB
                                         * address window, indexed by float bit patterns (no F2I, 32-bit address arithmetic) */
        VR5_SAMPLER_WINDOW = 5,         /* window layout only */
-       VR5_SAMPLER_HYBRID_WINDOW2 = 6 }; /* texture : window 1 : 2 */
+       VR5_SAMPLER_HYBRID_WINDOW2 = 6, /* texture : window 1 : 2 */
+       /* NOT a parity policy: GPURenderer4's semantics (GPURenderer4.cu:33-97) - trilinear volume fetch, linearly
+        * interpolated transfer function - evaluated in software fp32; 8 bytes per sample from an 8-byte-per-cell layout.
+        * Checked bit for bit against the restated CPU oracle (oracle_port.c, trilinear section), SURVEY 8(f) rank 2. */
+       VR5_SAMPLER_TRILINEAR = 16 };
 
 /* ---- lifecycle ------------------------------------------------------------------------------------------ */
 

@@ -101,6 +101,8 @@ class Port:
         L = self.lib
         L.orc_render_rows.argtypes = [C.POINTER(Raycaster), C.POINTER(C.c_uint8), C.c_int, C.c_int, C.POINTER(Counters)]
         L.orc_render_rows.restype = C.c_int
+        L.orc_render_rows_trilinear.argtypes = L.orc_render_rows.argtypes
+        L.orc_render_rows_trilinear.restype = C.c_int
         L.orc_default_base_tf.argtypes = [C.POINTER(C.c_float)]
         L.orc_premultiply_tf.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.orc_build_esl_bits.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_uint8), C.POINTER(C.c_uint32)]
@@ -114,8 +116,10 @@ class Port:
         L.orc_synth_cos_table.argtypes = [C.POINTER(C.c_int16)]
 
     # -- rendering ---------------------------------------------------------------------------------------
-    def render(self, scene: Scene, rows=None, threads: int | None = None):
-        """Frame (or row range) as uint8 [H, W, 4] plus summed counters; rows are split over host threads."""
+    def render(self, scene: Scene, rows=None, threads: int | None = None, trilinear: bool = False):
+        """Frame (or row range) as uint8 [H, W, 4] plus summed counters; rows are split over host threads.
+        trilinear=True: the restated GPURenderer4 sampler policy (fp32 trilinear volume fetch, linear TF)."""
+        fn = self.lib.orc_render_rows_trilinear if trilinear else self.lib.orc_render_rows
         w, h = scene.width, scene.height
         row0, row1 = (0, h) if rows is None else rows
         out = np.zeros((h, w, 4), dtype=np.uint8)
@@ -125,7 +129,7 @@ class Port:
 
         def work(span):
             cnt = Counters()
-            rc = self.lib.orc_render_rows(C.byref(scene.rc), _u8p(out), span[0], span[1], C.byref(cnt))
+            rc = fn(C.byref(scene.rc), _u8p(out), span[0], span[1], C.byref(cnt))
             if rc != 0:
                 raise RuntimeError("orc_render_rows returned %d" % rc)
             return cnt.as_dict()

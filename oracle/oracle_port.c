@@ -309,3 +309,149 @@ void orc_histogram(const uint8_t *data, uint64_t n, float *hist256) {
     }
     for (int i = 0; i < 256; i++) hist256[i] = hist256[i] / top;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Trilinear sampler policy: a CPU restatement of GPURenderer4's semantics
+ * (GPURenderer4.cu:33-97) with the texture unit's arithmetic written out in fp32.
+ *
+ * Parity status of THIS section: UNPINNED. GPURenderer4 needs legacy texture references (does not compile with
+ * CUDA 12) and its filtering runs in the texture unit's 9-bit fixed point, which no CPU code here
+ * reproduces. What is restated is the documented filtering formula evaluated in fp32, one rounding per
+ * operation, in the order written below; the CUDA trilinear kernel follows the same order and is compared bit
+ * for bit against this function, never against the nearest-neighbour parity bar.
+ *
+ *   volume:  tex3D(volume_texture, (p+1)*0.5) - normalised coordinates, linear filter, clamp, normalised-float
+ *            read mode (GPURenderer4.cu:76, :136-141): texel position t = u*n - 0.5, cell i0 = floor(t),
+ *            weight w = t - i0, neighbours clamped to [0, n-1], lerp x then y then z as a + w*(b - a) on the raw
+ *            byte values, result / 255.
+ *   TF:      tex1D(transfer_fn_texture, sample) - 128 entries, normalised, linear, clamp (GPURenderer4.cu:77,
+ *            :102-107): position s*128 - 0.5, lerp of the two entries per channel.
+ *   shading: GPURenderer4.cu:41-51: second trilinear sample at p + L*0.01, (sample_l - sample) * kd.
+ * ------------------------------------------------------------------------------------------------------- */
+static inline float lerp_f(float a, float b, float w) {
+    float d = b - a;
+    float m = w * d;
+    return a + m;
+}
+
+static inline void tri_axis(float p, uint32_t n, int64_t *i0, int64_t *i1, float *w) {
+    float shifted = p + 1.0f;
+    float unit = shifted * 0.5f;
+    float scaled = unit * (float)n;
+    float t = scaled - 0.5f;
+    float fl = floorf(t);
+    *w = t - fl;
+    int64_t a = (int64_t)fl, b = a + 1;
+    if (a < 0) a = 0;
+    if (a > (int64_t)n - 1) a = (int64_t)n - 1;
+    if (b < 0) b = 0;
+    if (b > (int64_t)n - 1) b = (int64_t)n - 1;
+    *i0 = a; *i1 = b;
+}
+
+static inline float fetch_trilinear(const vr5_model *m, float px, float py, float pz) {
+    int64_t x0, x1, y0, y1, z0, z1;
+    float wx, wy, wz;
+    tri_axis(px, m->dims.x, &x0, &x1, &wx);
+    tri_axis(py, m->dims.y, &y0, &y1, &wy);
+    tri_axis(pz, m->dims.z, &z0, &z1, &wz);
+    const uint64_t sx = m->dims.x, sxy = (uint64_t)m->dims.x * m->dims.y;
+#define VOX(X, Y, Z) ((float)m->data[(uint64_t)(Z) * sxy + (uint64_t)(Y) * sx + (uint64_t)(X)])
+    float c00 = lerp_f(VOX(x0, y0, z0), VOX(x1, y0, z0), wx);
+    float c10 = lerp_f(VOX(x0, y1, z0), VOX(x1, y1, z0), wx);
+    float c01 = lerp_f(VOX(x0, y0, z1), VOX(x1, y0, z1), wx);
+    float c11 = lerp_f(VOX(x0, y1, z1), VOX(x1, y1, z1), wx);
+#undef VOX
+    float c0 = lerp_f(c00, c10, wy);
+    float c1 = lerp_f(c01, c11, wy);
+    float c = lerp_f(c0, c1, wz);
+    return c / 255.0f;
+}
+
+static inline vr5_f4 classify_linear(const vr5_f4 *tf, float s) {
+    float scaled = s * (float)VR5_TF_SIZE;
+    float t = scaled - 0.5f;
+    float fl = floorf(t);
+    float w = t - fl;
+    int j0 = (int)fl, j1 = j0 + 1;
+    if (j0 < 0) j0 = 0;
+    if (j0 > VR5_TF_SIZE - 1) j0 = VR5_TF_SIZE - 1;
+    if (j1 < 0) j1 = 0;
+    if (j1 > VR5_TF_SIZE - 1) j1 = VR5_TF_SIZE - 1;
+    vr5_f4 a = tf[j0], b = tf[j1], c;
+    c.x = lerp_f(a.x, b.x, w); c.y = lerp_f(a.y, b.y, w); c.z = lerp_f(a.z, b.z, w); c.w = lerp_f(a.w, b.w, w);
+    return c;
+}
+
+static void cast_pixel_trilinear(const vr5_raycaster *r, uint8_t *rgba8, int col, int row, orc_counters *cnt) {
+    vr5_f3 o, d;
+    float k, k_far;
+    primary_ray(&r->view, col, row, &o, &d);
+    if (!clip_ray(&r->volume, o, d, &k, &k_far)) return;
+    cnt->rays_hit++;
+    float px, py, pz;
+#define ADVANCE_POINT()                                   \
+    do {                                                  \
+        float mx = d.x * k, my = d.y * k, mz = d.z * k;   \
+        px = o.x + mx; py = o.y + my; pz = o.z + mz;      \
+    } while (0)
+    ADVANCE_POINT();
+    while (k <= k_far) { /* GPURenderer4.cu:63-71: same empty-space loop, bitfield read through a texture there */
+        if (r->esl && block_is_empty(r, px, py, pz)) {
+            k += leap_distance(r, px, py, pz, d);
+            cnt->esl_iters++;
+        } else {
+            break;
+        }
+        k += r->ray_step;
+        ADVANCE_POINT();
+    }
+    if (k > k_far) return;
+    cnt->rays_accum++;
+    vr5_f4 acc = {0, 0, 0, 0};
+    while (k <= k_far) { /* GPURenderer4.cu:75-86 */
+        float sample = fetch_trilinear(&r->volume, px, py, pz);
+        vr5_f4 cur = classify_linear(r->transfer_fn, sample);
+        cnt->samples++;
+        if (cur.w > 0.05f && r->light_kd > 0.01f) { /* GPURenderer4.cu:41-51 shade_texture */
+            float lx = r->view.light_pos.x - px, ly = r->view.light_pos.y - py, lz = r->view.light_pos.z - pz;
+            float xx = lx * lx, yy = ly * ly, zz = lz * lz;
+            float s = xx + yy;
+            s = s + zz;
+            float inv = 1.0f / sqrtf(s);
+            float nx = lx * inv, ny = ly * inv, nz = lz * inv;
+            float ox = nx * 0.01f, oy = ny * 0.01f, oz = nz * 0.01f;
+            float qx = px + ox, qy = py + oy, qz = pz + oz;
+            float sample_l = fetch_trilinear(&r->volume, qx, qy, qz);
+            float diff = sample_l - sample;
+            diff = diff * r->light_kd;
+            cur.x += diff; cur.y += diff; cur.z += diff;
+            cnt->shaded++;
+        }
+        float t = 1 - acc.w;
+        float cx = cur.x * t, cy = cur.y * t, cz = cur.z * t, cw = cur.w * t;
+        acc.x = acc.x + cx; acc.y = acc.y + cy; acc.z = acc.z + cz; acc.w = acc.w + cw;
+        if (acc.w > r->ray_threshold) break;
+        k += r->ray_step;
+        ADVANCE_POINT();
+    }
+#undef ADVANCE_POINT
+    uint8_t *px8 = rgba8 + 4 * ((size_t)row * r->view.dims.x + (size_t)col);
+    px8[0] = (uint8_t)unit_to_index(acc.x, 256);
+    px8[1] = (uint8_t)unit_to_index(acc.y, 256);
+    px8[2] = (uint8_t)unit_to_index(acc.z, 256);
+    px8[3] = (uint8_t)unit_to_index(acc.w, 256);
+}
+
+int orc_render_rows_trilinear(const vr5_raycaster *r, uint8_t *rgba8, int row0, int row1, orc_counters *cnt) {
+    if (r->volume.data == NULL || r->transfer_fn == NULL || r->esl_volume == NULL || rgba8 == NULL) return 1;
+    orc_counters local = {0, 0, 0, 0, 0};
+    int w = r->view.dims.x, h = r->view.dims.y;
+    if (row0 < 0) row0 = 0;
+    if (row1 > h) row1 = h;
+    if (row1 > row0) memset(rgba8 + (size_t)row0 * w * 4, 0, (size_t)(row1 - row0) * w * 4);
+    for (int row = row0; row < row1; row++)
+        for (int col = 0; col < w; col++) cast_pixel_trilinear(r, rgba8, col, row, &local);
+    if (cnt) *cnt = local;
+    return 0;
+}

@@ -1,0 +1,81 @@
+"""Trilinear sampler policy: GPURenderer4's semantics evaluated in software fp32.
+
+The CPU side is oracle_port.c's trilinear section ("parity unpinned": GPURenderer4 cannot be built with CUDA 12 and its
+filtering runs in the texture unit's fixed point). The CUDA policy VR5_SAMPLER_TRILINEAR performs the same fp32 operations
+in the same order and is held to bit equality with that restatement."""
+import numpy as np
+import pytest
+
+import oracle
+from common import POSES, assert_parity, golden_scene, product_scene, tf_by_name
+
+
+def test_oracle_trilinear_reduces_to_nearest_on_constant_data(port, R):
+    """Property pin of the restatement: with a constant volume every trilinear fetch is v/255 exactly, and with a constant
+    transfer function classification cannot depend on the sampler - so both policies must give the same frame."""
+    vol = np.full((24, 24, 24), 137, dtype=np.uint8)
+    base = np.tile(np.array([0.3, 0.6, 0.9, 0.02], dtype=np.float32), (128, 1))
+    ref_view = oracle.View.from_buffer_copy(bytes(R.camera(96, 64, 0, (10.0, 25.0, 0.0), 2.0)))  # host-side camera builder
+    sc = port.make_scene(vol, base, ref_view, light_kd=0.0, esl=False)
+    near, cn = port.render(sc)
+    tri, ct = port.render(sc, trilinear=True)
+    assert np.array_equal(near, tri) and cn == ct and cn["samples"] > 0
+
+
+def test_oracle_trilinear_is_smooth_where_nearest_steps(port, bucky, golden):
+    """The trilinear frame differs from the nearest one on real data, but by little: the same scene, same counters class."""
+    case = next(c for c in golden["cases"] if c["name"] == "bucky_ortho_0_0_0")
+    sc = golden_scene(port, case, bucky)
+    near, cn = port.render(sc)
+    tri, ct = port.render(sc, trilinear=True)
+    assert cn["rays_hit"] == ct["rays_hit"] and cn["esl_iters"] == ct["esl_iters"]
+    d = np.abs(near.astype(np.int16) - tri.astype(np.int16))
+    assert 0 < d.max() and d.mean() < 12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["bucky_ortho_0_0_0", "bucky_persp_-45_-45_0", "synthA64_default_persp"])
+def test_gpu_trilinear_matches_restated_oracle(name, golden, port, volumes, R):
+    case = next(c for c in golden["cases"] if c["name"] == name)
+    sc = golden_scene(port, case, volumes(case["volume"]))
+    scene, params = product_scene(R, sc)
+    gpu = R.GPURenderer5(0, sampler="trilinear")
+    try:
+        gpu.set_window_buffer(case["width"], case["height"])
+        gpu.set_scene(scene)
+        frame = gpu.render_volume(params)
+        want, cnt = port.render(sc, trilinear=True)
+        assert_parity(frame, want, exact=True, what=name)
+        assert gpu.last_variant() == 16
+        assert gpu.count(params) == cnt
+    finally:
+        gpu.close()
+
+
+@pytest.mark.gpu
+def test_gpu_trilinear_ragged_random(port, R):
+    """Non-cubic random volume (worst case for interpolation: neighbours uncorrelated), ragged viewports, every TF preset,
+    both projections, shading on and off, partition strips."""
+    rng = np.random.default_rng(5)
+    vol = rng.integers(0, 256, size=(29, 41, 66), dtype=np.uint8)
+    vol[:, :13] = 0
+    gpu = R.GPURenderer5(0, sampler="trilinear")
+    try:
+        for tf_name, kw in [("default", {}), ("opaque", {}), ("semi", {"ray_threshold": 1.0, "light_kd": 0.0}), ("default", {"esl": False})]:
+            base = {"default": R.default_base_tf(), "opaque": R.tf_opaque(), "semi": R.tf_semi(66)}[tf_name]
+            bd, mm, bs = R.build_minmax(vol)
+            tf = R.premultiply_tf(base)
+            scene = R.Scene(vol, tf, R.build_esl_bits(tf, mm), bd, bs, R.default_ray_step(66, 41, 29), **kw)
+            gpu.set_scene(scene)
+            for persp, ang, wh in [(0, POSES[1], (163, 97)), (1, (20, 130, 0), (129, 131)), (1, POSES[3], (8, 4))]:
+                view = R.camera(wh[0], wh[1], persp, ang, 2.0)
+                gpu.set_window_buffer(*wh)
+                params = scene.params(view)
+                frame = gpu.render_volume(params)
+                osc = port.make_scene(vol, tf_by_name(port, tf_name, 66), oracle.View.from_buffer_copy(bytes(view)),
+                                      threshold=scene.ray_threshold, esl=scene.esl, light_kd=scene.light_kd)
+                want, cnt = port.render(osc, trilinear=True)
+                assert_parity(frame, want, exact=True, what=(tf_name, persp, ang))
+                assert gpu.count(params) == cnt
+    finally:
+        gpu.close()

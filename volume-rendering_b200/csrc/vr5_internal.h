@@ -28,6 +28,7 @@ struct vr5_renderer {
     int last_variant = -1;  // SAMPLER template id of the last cast_kernel launch
     uint8_t *d_vol_brick = nullptr;
     uint8_t *d_vol_padded = nullptr;  // (nx+1)(ny+1)(nz+1), edge replicated: unclamped LDG path
+    uint8_t *d_cells = nullptr;       // trilinear policy: 8-byte cell records, (nx+1)(ny+1)(nz+1) of them (vr5_tri.cuh)
     uint8_t *d_vol_window = nullptr;  // window layout (fetch mode 4), NULL when the volume does not fit one 4-GiB window
     uint32_t win_hi = 0, win_sx = 0, win_sxy = 0;
     float win_mx = 0, win_my = 0, win_mz = 0;

@@ -15,6 +15,7 @@
 
 #include "../../include/vr5.h"
 #include "vr5_cast.cuh"
+#include "vr5_tri.cuh"
 #include "vr5_internal.h"
 
 using namespace vr5;
@@ -85,6 +86,23 @@ __global__ void p2_layout_kernel(const uint8_t *__restrict__ lin, uint8_t *__res
         const uint64_t row = i / sx;
         const int x = (int)(i % sx) - origin, y = (int)(row % rows) - origin, z = (int)(row / rows) - origin;
         win[i] = lin[((uint64_t)min(max(z, 0), (int)nz - 1) * ny + min(max(y, 0), (int)ny - 1)) * nx + min(max(x, 0), (int)nx - 1)];
+    }
+}
+
+// linear -> trilinear cells (vr5_tri.cuh): record (jx, jy, jz) = the eight voxels around cell i0 = j - 1, clamped to the grid;
+// byte b of the 8-byte record is the neighbour with offsets (b & 1, (b >> 1) & 1, b >> 2)
+__global__ void cell_layout_kernel(const uint8_t *__restrict__ lin, uint2 *__restrict__ cells, uint32_t nx, uint32_t ny, uint32_t nz) {
+    const uint32_t cx = nx + 1, cy = ny + 1, cz = nz + 1;
+    const uint64_t n = (uint64_t)cx * cy * cz;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const int x0 = (int)(i % cx) - 1, y0 = (int)((i / cx) % cy) - 1, z0 = (int)(i / ((uint64_t)cx * cy)) - 1;
+        uint32_t w[2] = {0u, 0u};
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            const int x = min(max(x0 + (b & 1), 0), (int)nx - 1), y = min(max(y0 + ((b >> 1) & 1), 0), (int)ny - 1), z = min(max(z0 + (b >> 2), 0), (int)nz - 1);
+            w[b >> 2] |= (uint32_t)lin[((uint64_t)z * ny + y) * nx + x] << (8 * (b & 3));
+        }
+        cells[i] = make_uint2(w[0], w[1]);
     }
 }
 
@@ -213,6 +231,7 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
         else if (!strcmp(env, "hybridw") || !strcmp(env, "4")) r->sampler = VR5_SAMPLER_HYBRID_WINDOW;
         else if (!strcmp(env, "window") || !strcmp(env, "5")) r->sampler = VR5_SAMPLER_WINDOW;
         else if (!strcmp(env, "hybridw2") || !strcmp(env, "6")) r->sampler = VR5_SAMPLER_HYBRID_WINDOW2;
+        else if (!strcmp(env, "trilinear") || !strcmp(env, "16")) r->sampler = VR5_SAMPLER_TRILINEAR;
     }
     *out = r;
     return 0;
@@ -268,6 +287,7 @@ static void free_layouts(vr5_renderer *r) {
     if (r->d_vol_brick) { cudaFree(r->d_vol_brick); r->d_vol_brick = nullptr; }
     if (r->d_vol_padded) { cudaFree(r->d_vol_padded); r->d_vol_padded = nullptr; }
     if (r->d_vol_window) { cudaFree(r->d_vol_window); r->d_vol_window = nullptr; }
+    if (r->d_cells) { cudaFree(r->d_cells); r->d_cells = nullptr; }
     free_p2(r);
 }
 
@@ -470,6 +490,16 @@ static int build_p2(vr5_renderer *r) {
 static int build_layout(vr5_renderer *r) {
     free_layouts(r);
     if (!r->d_vol_linear) return 0;
+    if (r->sampler == VR5_SAMPLER_TRILINEAR) {
+        const uint64_t bytes = (uint64_t)(r->nx + 1) * (r->ny + 1) * (r->nz + 1) * 8u;
+        cudaError_t e = cudaMalloc(&r->d_cells, bytes);
+        if (e != cudaSuccess) { r->d_cells = nullptr; vr5_fail(r, "cudaMalloc trilinear cells (8 bytes per voxel)", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
+        cell_layout_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, reinterpret_cast<uint2 *>(r->d_cells), r->nx, r->ny, r->nz);
+        r->launches++;
+        VR5_CUDA(r, cudaGetLastError());
+        VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+        return 0;
+    }
     if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW) {
         if (!getenv("VR5_NO_P2") && build_p2(r)) return 1;
         if (!r->p2_wl && build_window(r)) return 1;
@@ -577,10 +607,10 @@ extern "C" int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes
 
 extern "C" int vr5_set_sampler(vr5_renderer *r, int sampler) {
     if (!r) return 1;
-    if (sampler < 0 || sampler > VR5_SAMPLER_HYBRID_WINDOW2) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (sampler < 0 || (sampler > VR5_SAMPLER_HYBRID_WINDOW2 && sampler != VR5_SAMPLER_TRILINEAR)) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     VR5_CUDA(r, sync_all(r));
-    if (sampler == r->sampler && (r->d_vol_padded || r->d_vol_brick || r->tex || r->d_vol_window || r->p2_wl || !r->d_vol_linear)) return 0;
+    if (sampler == r->sampler && (r->d_vol_padded || r->d_vol_brick || r->tex || r->d_vol_window || r->p2_wl || r->d_cells || !r->d_vol_linear)) return 0;
     r->sampler = sampler;
     return build_layout(r);
 }
@@ -743,6 +773,30 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
     // the padded layouts may be indexed without the upper clamp when rays are clipped to the cube they cover
     const bool cube = a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f;
     cudaError_t e;
+    if (r->sampler == VR5_SAMPLER_TRILINEAR) {  // GPURenderer4 semantics in software fp32 (vr5_tri.cuh)
+        TriArgs t;
+        t.cells = reinterpret_cast<const uint2 *>(r->d_cells);
+        t.cx = r->nx + 1; t.cy = r->ny + 1;
+        t.nfx = (float)r->nx; t.nfy = (float)r->ny; t.nfz = (float)r->nz;
+        t.nx = r->nx; t.ny = r->ny; t.nz = r->nz;
+        int &per_sm = r->ctas_per_sm[count ? 254 : 255];
+        if (per_sm == 0) {
+            e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tri_kernel<true>, kCtaThreads, 0)
+                      : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tri_kernel<false>, kCtaThreads, 0);
+            if (e != cudaSuccess || per_sm < 1) per_sm = 1;
+        }
+        uint32_t grid = (uint32_t)(r->num_sms * per_sm);
+        const uint32_t needed = (a.n_queue + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
+        if (grid > needed) grid = needed ? needed : 1;
+        if (count) tri_kernel<true><<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
+        else tri_kernel<false><<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
+        r->last_grid = grid;
+        r->launches++;
+        r->last_variant = VR5_SAMPLER_TRILINEAR;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) { vr5_fail(r, "tri_kernel launch", e, __FILE__, __LINE__); return 1; }
+        return 0;
+    }
     // power-of-two specialisation of the window policies (the instrumented variant counts through the generic kernels:
     // work counters do not depend on the memory path)
     if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW && r->p2_wl && !count && cube && window_ok(r, a)) {
