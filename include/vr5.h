@@ -219,6 +219,25 @@ int vr5_build_minmax_device(vr5_renderer *r, uint16_t *esl_block_dims, uint8_t *
 /* ModelBase::compute_histogram (ModelBase.cpp:19-33) on the device from the current volume: 256 normalised bins */
 int vr5_histogram_device(vr5_renderer *r, float *hist256);
 
+/* ---- volume files (host side; SURVEY 8(f) rank 3: ddsbase.cpp, ModelBase.cpp:35-109) ------------------------ */
+
+/* readPVMvolume (ddsbase.cpp:343-435): PVM / PVM2 / PVM3 container, DDS-compressed ("DDS v3d" / "DDS v3e") or plain.
+ * *data (malloc, release with vr5_volume_free) receives width*height*depth*components bytes, x fastest. 0 ok / 1 error
+ * (never exits, unlike the reference's ERRORMSG); message in vr5_volume_io_error(). scale_xyz may be NULL. */
+int vr5_load_pvm(const char *path, uint8_t **data, uint32_t *width, uint32_t *height, uint32_t *depth, uint32_t *components,
+                 float *scale_xyz);
+/* ModelBase::load_model's RAW branch (ModelBase.cpp:66-84); the dimensions the reference prompts for are arguments */
+int vr5_load_raw(const char *path, uint32_t width, uint32_t height, uint32_t depth, uint32_t components, uint8_t **data);
+/* quantize() (ddsbase.cpp:475-558): 16-bit big-endian voxels to 8 bit, linear or the reference's non-linear mapping */
+int vr5_quantize16(const uint8_t *data16_be, uint32_t width, uint32_t height, uint32_t depth, int linear, uint8_t **data8);
+/* ModelBase::load_model for a .pvm file: decode, quantise 2-component data, refuse more (ModelBase.cpp:85-93) */
+int vr5_load_volume(const char *path, uint8_t **data8, uint32_t *width, uint32_t *height, uint32_t *depth);
+/* the Differential Data Stream itself (ddsbase.cpp:187-245), magic included; the encoder exists for tests and tools */
+int vr5_dds_decode(const uint8_t *stream, uint64_t bytes, uint8_t **out, uint64_t *out_bytes);
+int vr5_dds_encode(const uint8_t *data, uint64_t bytes, uint32_t skip, uint32_t strip, int v3e, uint8_t **out, uint64_t *out_bytes);
+void vr5_volume_free(void *p);
+const char *vr5_volume_io_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -248,6 +248,25 @@ class Ref:
         L.ref_render_rows.restype = C.c_int
         assert L.ref_sizeof_raycaster() == 160 and L.ref_sizeof_view() == 68 and L.ref_sizeof_model() == 32
 
+    def read_pvm(self, path: str) -> np.ndarray:
+        """The reference's own readPVMvolume: voxels [D, H, W, components]."""
+        w, h, d, nc = C.c_uint(), C.c_uint(), C.c_uint(), C.c_uint()
+        self.lib.ref_read_pvm.argtypes = [C.c_char_p, C.POINTER(C.c_uint8), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.POINTER(C.c_uint)]
+        if self.lib.ref_read_pvm(path.encode(), None, C.byref(w), C.byref(h), C.byref(d), C.byref(nc)) != 0:
+            raise RuntimeError("reference readPVMvolume failed on " + path)
+        out = np.zeros((d.value, h.value, w.value, nc.value), dtype=np.uint8)
+        self.lib.ref_read_pvm(path.encode(), _u8p(out), C.byref(w), C.byref(h), C.byref(d), C.byref(nc))
+        return out
+
+    def quantize16(self, data16_be: np.ndarray, w: int, h: int, d: int, linear: bool = False) -> np.ndarray:
+        """The reference's own quantize()."""
+        src = np.ascontiguousarray(data16_be, dtype=np.uint8)
+        out = np.zeros((d, h, w), dtype=np.uint8)
+        self.lib.ref_quantize16.argtypes = [C.POINTER(C.c_uint8), C.c_uint, C.c_uint, C.c_uint, C.c_int, C.POINTER(C.c_uint8)]
+        if self.lib.ref_quantize16(_u8p(src), w, h, d, 1 if linear else 0, _u8p(out)) != 0:
+            raise RuntimeError("reference quantize failed")
+        return out
+
     def load_model(self, path: str) -> int:
         return self.lib.ref_load_model(path.encode())
 

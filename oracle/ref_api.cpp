@@ -10,7 +10,8 @@
  *   - per-frame           VolR.cpp:98-113   (RaycasterBase::set_view(ViewBase::view); render_volume)
  *   - benchmark poses     VolR.cpp:225-253  (toggle_perspective(true); set_camera_position(a, 2))
  *
- * `#include "CPURenderer.cpp"` pulls the reference's own translation unit in verbatim so that the
+ * `#include "ddsbase.h"
+#include "CPURenderer.cpp"` pulls the reference's own translation unit in verbatim so that the
  * file-static `render_ray` (CPURenderer.cpp:11-41) can also be driven over a row range
  * (ref_render_rows) - same per-pixel code, different loop bounds - which the CPU-baseline timing
  * needs for bounded samples.
@@ -116,6 +117,25 @@ int ref_render_rows(const void *raycaster160, unsigned char *rgba8, int row0, in
     for (int row = row0; row < row1; row++)
         for (int col = 0; col < r.view.dims.x; col++)
             render_ray(r, buffer, make_short2(col, row));
+    return 0;
+}
+
+/* ddsbase.cpp:343-435 readPVMvolume as is: voxels only are copied out (caller's buffer of w*h*d*components bytes; pass
+ * NULL to query the dimensions). Returns 0 ok / 1 not readable. */
+int ref_read_pvm(const char *path, unsigned char *out, unsigned *w, unsigned *h, unsigned *d, unsigned *components) {
+    unsigned char *v = readPVMvolume(path, w, h, d, components, NULL, NULL, NULL, NULL, NULL, NULL, NULL);
+    if (v == NULL) return 1;
+    if (out != NULL) memcpy(out, v, (size_t)*w * *h * *d * *components);
+    free(v);
+    return 0;
+}
+
+/* ddsbase.cpp:475-558 quantize as is (nofree = TRUE: the caller keeps its 16-bit buffer) */
+int ref_quantize16(const unsigned char *data16_be, unsigned w, unsigned h, unsigned d, int linear, unsigned char *out8) {
+    unsigned char *q = quantize((unsigned char *)data16_be, w, h, d, linear ? TRUE : FALSE, TRUE);
+    if (q == NULL) return 1;
+    memcpy(out8, q, (size_t)w * h * d);
+    free(q);
     return 0;
 }
 

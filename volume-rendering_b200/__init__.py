@@ -118,6 +118,14 @@ def lib() -> C.CDLL:
         "vr5_peer_status": (C.c_int, [vp]),
         "vr5_peer_close": (None, [vp]),
         "vr5_synth_volume": (C.c_int, [vp, C.c_int, C.c_uint16, C.c_uint32]),
+        "vr5_load_pvm": (C.c_int, [C.c_char_p, C.POINTER(u8p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), f32p]),
+        "vr5_load_raw": (C.c_int, [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(u8p)]),
+        "vr5_quantize16": (C.c_int, [u8p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(u8p)]),
+        "vr5_load_volume": (C.c_int, [C.c_char_p, C.POINTER(u8p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+        "vr5_dds_decode": (C.c_int, [u8p, C.c_uint64, C.POINTER(u8p), C.POINTER(C.c_uint64)]),
+        "vr5_dds_encode": (C.c_int, [u8p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(u8p), C.POINTER(C.c_uint64)]),
+        "vr5_volume_free": (None, [vp]),
+        "vr5_volume_io_error": (C.c_char_p, []),
         "vr5_scene_default_base_tf": (None, [f32p]),
         "vr5_scene_premultiply_tf": (None, [f32p, f32p]),
         "vr5_scene_build_minmax": (None, [u8p, C.c_uint16, C.c_uint16, C.c_uint16, C.POINTER(C.c_uint16), u8p, C.POINTER(F3)]),

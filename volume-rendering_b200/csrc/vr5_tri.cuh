@@ -30,6 +30,10 @@ __device__ __forceinline__ void tri_axis(float p, float nf, uint32_t n, uint32_t
     j = (uint32_t)min(max(i0 + 1, 0), (int)n);                 // record index; clamps both neighbours like the oracle
 }
 
+__device__ __forceinline__ float byte_to_float(uint32_t word, int i) {
+    return fsub(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u + (uint32_t)i)), 8388608.0f);
+}
+
 __device__ __forceinline__ float lerp_rn(float a, float b, float w) { return fadd(a, fmul(w, fsub(b, a))); }
 
 // oracle fetch_trilinear: lerp x, then y, then z on the raw byte values, result / 255
@@ -41,8 +45,10 @@ __device__ __forceinline__ float tri_fetch(const TriArgs &t, float px, float py,
     tri_axis(pz, t.nfz, t.nz, jz, wz);
     const uint64_t rec = ((uint64_t)jz * t.cy + jy) * t.cx + jx;
     const uint2 c = __ldg(t.cells + rec);
-    const float v000 = (float)(c.x & 0xffu), v100 = (float)((c.x >> 8) & 0xffu), v010 = (float)((c.x >> 16) & 0xffu), v110 = (float)(c.x >> 24);
-    const float v001 = (float)(c.y & 0xffu), v101 = (float)((c.y >> 8) & 0xffu), v011 = (float)((c.y >> 16) & 0xffu), v111 = (float)(c.y >> 24);
+    // byte -> float without the conversion unit (I2F runs at 1/8 rate): drop the byte into the mantissa of 2^23 with one
+    // PRMT, subtract 2^23 (exact)
+    const float v000 = byte_to_float(c.x, 0), v100 = byte_to_float(c.x, 1), v010 = byte_to_float(c.x, 2), v110 = byte_to_float(c.x, 3);
+    const float v001 = byte_to_float(c.y, 0), v101 = byte_to_float(c.y, 1), v011 = byte_to_float(c.y, 2), v111 = byte_to_float(c.y, 3);
     const float c00 = lerp_rn(v000, v100, wx), c10 = lerp_rn(v010, v110, wx);
     const float c01 = lerp_rn(v001, v101, wx), c11 = lerp_rn(v011, v111, wx);
     const float c0 = lerp_rn(c00, c10, wy), c1 = lerp_rn(c01, c11, wy);

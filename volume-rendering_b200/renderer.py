@@ -282,3 +282,61 @@ class GPURenderer5:
         h = np.zeros(256, dtype=np.float32)
         self._check(self._L.vr5_histogram_device(self._h, _f32p(h)))
         return h
+
+
+# ---- volume files (include/vr5.h "volume files"; host side) ---------------------------------------------------------------
+def _take(ptr, nbytes) -> np.ndarray:
+    out = np.ctypeslib.as_array(ptr, shape=(nbytes,)).copy() if nbytes else np.zeros(0, dtype=np.uint8)
+    lib().vr5_volume_free(C.cast(ptr, C.c_void_p))
+    return out
+
+
+def _io_check(rc):
+    if rc != 0:
+        raise Vr5Error(lib().vr5_volume_io_error().decode())
+
+
+def load_pvm(path: str):
+    """readPVMvolume: (voxels [D, H, W, components] uint8, (sx, sy, sz))."""
+    p = C.POINTER(C.c_uint8)()
+    w, h, d, nc = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+    scale = (C.c_float * 3)()
+    _io_check(lib().vr5_load_pvm(path.encode(), C.byref(p), C.byref(w), C.byref(h), C.byref(d), C.byref(nc), scale))
+    vox = _take(p, w.value * h.value * d.value * nc.value)
+    return vox.reshape(d.value, h.value, w.value, nc.value), tuple(scale)
+
+
+def load_volume(path: str) -> np.ndarray:
+    """ModelBase::load_model for .pvm: 8-bit volume [D, H, W] (two-component data quantised, more refused)."""
+    p = C.POINTER(C.c_uint8)()
+    w, h, d = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    _io_check(lib().vr5_load_volume(path.encode(), C.byref(p), C.byref(w), C.byref(h), C.byref(d)))
+    return _take(p, w.value * h.value * d.value).reshape(d.value, h.value, w.value)
+
+
+def load_raw(path: str, w: int, h: int, d: int, components: int = 1) -> np.ndarray:
+    p = C.POINTER(C.c_uint8)()
+    _io_check(lib().vr5_load_raw(path.encode(), w, h, d, components, C.byref(p)))
+    return _take(p, w * h * d * components).reshape(d, h, w, components)
+
+
+def quantize16(data16_be: np.ndarray, w: int, h: int, d: int, linear: bool = False) -> np.ndarray:
+    src = np.ascontiguousarray(data16_be, dtype=np.uint8)
+    assert src.size == 2 * w * h * d
+    p = C.POINTER(C.c_uint8)()
+    _io_check(lib().vr5_quantize16(_u8p(src), w, h, d, 1 if linear else 0, C.byref(p)))
+    return _take(p, w * h * d).reshape(d, h, w)
+
+
+def dds_decode(stream: bytes) -> bytes:
+    src = np.frombuffer(stream, dtype=np.uint8)
+    p, n = C.POINTER(C.c_uint8)(), C.c_uint64()
+    _io_check(lib().vr5_dds_decode(_u8p(src), src.size, C.byref(p), C.byref(n)))
+    return _take(p, n.value).tobytes()
+
+
+def dds_encode(data: bytes, skip: int = 1, strip: int = 1, v3e: bool = False) -> bytes:
+    src = np.frombuffer(data, dtype=np.uint8)
+    p, n = C.POINTER(C.c_uint8)(), C.c_uint64()
+    _io_check(lib().vr5_dds_encode(_u8p(src), src.size, skip, strip, 1 if v3e else 0, C.byref(p), C.byref(n)))
+    return _take(p, n.value).tobytes()
