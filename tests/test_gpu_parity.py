@@ -14,6 +14,7 @@ import oracle
 from common import POSES, assert_parity, golden_scene, product_scene, sha, tf_by_name
 
 pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 # kernel variant ids a sampler policy may run as: the window policies switch to their power-of-two specialisations (7..9)
 # when every volume dimension is a power of two (vr5_cast.cuh)
 VARIANT_OF = {"linear": {0}, "brick": {1}, "tex3d": {2}, "hybrid": {3}, "hybridw": {4, 7}, "window": {5, 8}, "hybridw2": {6, 9}}
@@ -179,3 +180,14 @@ def test_error_behaviour(R):
     p.view.dims[0] = 32
     assert r._L.vr5_render(r._h, p, out.ctypes.data, 0) == 1 and "dims" in r.last_error()
     r.close()
+
+
+def test_reference_benchmark_sweep_matches_oracle():
+    """tools/volr_suite.py --check: the reference's 24-configuration benchmark matrix (VolR.cpp:225-321: datasets, ERT / ESL
+    toggles, viewport scales 0.9..0.3, ray step x1.1..x1.7; 2 projections x 4 poses each), every frame equal to the oracle."""
+    import subprocess
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "volr_suite.py"), "--n", "48", "--window", "200", "150", "--check", "--reps", "1"],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "24 configurations, 192 frames, all equal to the CPU oracle" in out.stdout
