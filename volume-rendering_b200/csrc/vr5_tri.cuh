@@ -1,5 +1,5 @@
 // vr5_tri.cuh - trilinear sampler policy (GPURenderer4 semantics, GPURenderer4.cu:33-97) as software
-// fp32 arithmetic: every operation of oracle/oracle_port.c's trilinear restatement, in the same order, through the exact
+// fp32 arithmetic: every operation of the CPU checker's trilinear restatement (test infrastructure, never linked here), in the same order, through the exact
 // __f*_rn helpers of vr5_cast.cuh. Compared bit for bit with that restatement, never with the nearest-neighbour parity bar.
 //
 // Memory layout ("cells"): one 8-byte record per cell (i0x, i0y, i0z) in [-1, n-1]^3 holding the eight voxels the cell's
