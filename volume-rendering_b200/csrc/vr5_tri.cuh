@@ -36,15 +36,23 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, int i) {
 
 __device__ __forceinline__ float lerp_rn(float a, float b, float w) { return fadd(a, fmul(w, fsub(b, a))); }
 
-// oracle fetch_trilinear: lerp x, then y, then z on the raw byte values, result / 255
-__device__ __forceinline__ float tri_fetch(const TriArgs &t, float px, float py, float pz) {
+// request the cell record of a point (the load) and keep its three weights
+struct TriTap { uint2 c; float wx, wy, wz; };
+__device__ __forceinline__ TriTap tri_request(const TriArgs &t, float px, float py, float pz) {
     uint32_t jx, jy, jz;
-    float wx, wy, wz;
-    tri_axis(px, t.nfx, t.nx, jx, wx);
-    tri_axis(py, t.nfy, t.ny, jy, wy);
-    tri_axis(pz, t.nfz, t.nz, jz, wz);
+    TriTap tap;
+    tri_axis(px, t.nfx, t.nx, jx, tap.wx);
+    tri_axis(py, t.nfy, t.ny, jy, tap.wy);
+    tri_axis(pz, t.nfz, t.nz, jz, tap.wz);
     const uint64_t rec = ((uint64_t)jz * t.cy + jy) * t.cx + jx;
-    const uint2 c = __ldg(t.cells + rec);
+    tap.c = __ldg(t.cells + rec);
+    return tap;
+}
+
+// oracle fetch_trilinear: lerp x, then y, then z on the raw byte values, result / 255
+__device__ __forceinline__ float tri_resolve(const TriTap &tap) {
+    const uint2 c = tap.c;
+    const float wx = tap.wx, wy = tap.wy, wz = tap.wz;
     // byte -> float without the conversion unit (I2F runs at 1/8 rate): drop the byte into the mantissa of 2^23 with one
     // PRMT, subtract 2^23 (exact)
     const float v000 = byte_to_float(c.x, 0), v100 = byte_to_float(c.x, 1), v010 = byte_to_float(c.x, 2), v110 = byte_to_float(c.x, 3);
@@ -54,6 +62,8 @@ __device__ __forceinline__ float tri_fetch(const TriArgs &t, float px, float py,
     const float c0 = lerp_rn(c00, c10, wy), c1 = lerp_rn(c01, c11, wy);
     return fdiv(lerp_rn(c0, c1, wz), 255.0f);
 }
+
+__device__ __forceinline__ float tri_fetch(const TriArgs &t, float px, float py, float pz) { return tri_resolve(tri_request(t, px, py, pz)); }
 
 // oracle classify_linear: 128-entry table, position s * 128 - 0.5, clamp, per-channel lerp
 __device__ __forceinline__ float4 tri_classify(const float4 *s_tf, float s) {
@@ -124,8 +134,14 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
     if (COUNT) cnt.rays_accum++;
     if (!(k <= k_far)) return 0u;
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
+    // software pipelined like the nearest path: the cell of sample i + 1 is requested before sample i is interpolated and
+    // composited (speculative past k_far: the record index is clamped, so the load is always in bounds)
+    TriTap tap = tri_request(t, px, py, pz);
     while (k <= k_far) {  // GPURenderer4.cu:75-86
-        const float s = tri_fetch(t, px, py, pz);
+        const float kn = fadd(k, step);
+        const float nx = fadd(ox, fmul(dx, kn)), ny = fadd(oy, fmul(dy, kn)), nz = fadd(oz, fmul(dz, kn));
+        const TriTap next = tri_request(t, nx, ny, nz);
+        const float s = tri_resolve(tap);
         float4 c = tri_classify(s_tf, s);
         if (COUNT) cnt.samples++;
         if (c.w > a.shade_alpha) {  // GPURenderer4.cu:78 guard, :41-51 shade_texture
@@ -142,8 +158,7 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
         const float tr = fsub(1.0f, aa);
         ar = fadd(ar, fmul(c.x, tr)); ag = fadd(ag, fmul(c.y, tr)); ab = fadd(ab, fmul(c.z, tr)); aa = fadd(aa, fmul(c.w, tr));
         if (aa > a.threshold) break;
-        k = fadd(k, step);
-        px = fadd(ox, fmul(dx, k)); py = fadd(oy, fmul(dy, k)); pz = fadd(oz, fmul(dz, k));
+        k = kn; px = nx; py = ny; pz = nz; tap = next;
     }
     return trunc_clamp(fmul(ar, 256.0f), 255u) | (trunc_clamp(fmul(ag, 256.0f), 255u) << 8) |
            (trunc_clamp(fmul(ab, 256.0f), 255u) << 16) | (trunc_clamp(fmul(aa, 256.0f), 255u) << 24);
