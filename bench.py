@@ -192,7 +192,8 @@ def run_reference_arm(args, wl):
     threads = os.cpu_count() or 1
     cpu = CpuReference(wl)
     est_frame_core_s = 11.0 * (wl["n"] / 512.0) * (wl["w"] * wl["h"]) / (1920.0 * 1080.0)
-    every = max(1, int(round(est_frame_core_s / (4.0 * threads))))
+    # rows are rendered twice per step (timed, then counted): keep the whole --steps/--warmup run near 90 s of wall clock
+    every = max(1, int(round(est_frame_core_s * 2.0 * (args.steps + args.warmup) / threads / 90.0)))
     spans = strip_spans(wl["h"], every)
     frac = sum(b - a for a, b in spans) / wl["h"]
     out = np.zeros((wl["h"], wl["w"], 4), dtype=np.uint8)
