@@ -91,6 +91,7 @@ struct KArgs {
                              // so the host knows the next base without touching the device (vr5_render.cu, launch)
     uint32_t n_queue;        // padded tile count
     uint32_t tiles_x, tile_rows_local, groups_x;
+    int cta_fetch;           // 1: a CTA takes 8 queue slots at a time (one barrier per block), 0: every warp takes its own
     Counters *counters;
 };
 
@@ -429,18 +430,29 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
     if (SAMPLER >= 4) win = Window{pinned->wmx, pinned->wmy, pinned->wmz, pinned->whi, pinned->wsx, pinned->wsxy};
     const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_lut);
     Counters cnt = {0, 0, 0, 0, 0};
+    __shared__ unsigned s_q;
     for (;;) {
         unsigned q = 0;
-        if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
-        q = __shfl_sync(0xffffffffu, q, 0);
+        if (a.cta_fetch) {
+            // the CTA takes 8 consecutive queue slots at once = a 32x8-pixel block (queue groups are 4 tiles wide): its 8
+            // warps march through neighbouring voxels in step and share L1 lines (C3: 0.606 -> 0.596 ms). The price is a
+            // barrier per block, so the host only asks for it when rays of neighbouring tiles end together (no opaque TF
+            // entry: C4 measured 5 % slower with it). Same counter arithmetic as one slot per warp.
+            __syncthreads();
+            if (threadIdx.x == 0) s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
+            __syncthreads();
+            q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
+        } else {
+            if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
+            q = __shfl_sync(0xffffffffu, q, 0);
+        }
         if (q >= a.n_queue) break;
         const uint32_t group = q >> (kGroupLog2X + kGroupLog2Y), within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);
         const uint32_t tx = ((group % a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
         const uint32_t tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
-        if (tx >= a.tiles_x || tyl >= a.tile_rows_local) continue;
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
-        if (col < a.width && row < a.height) {  // ragged right / bottom edge: lanes outside the image idle
+        if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle
             const uint32_t rgba = cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, vs, win, lut_addr, s_esl, step, threshold, col, row, cnt);
             if (!COUNT) {
                 const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;

@@ -19,6 +19,7 @@ struct vr5_renderer {
     float *d_tf = nullptr;        // 128 x float4, pre-multiplied
     uint32_t *d_esl = nullptr;    // 1024 words
     bool have_tf = false;
+    bool tf_opaque = false;       // some TF entry has alpha >= 0.999 (a single sample can terminate a ray)
     bool tf_can_shade = false;    // some TF entry has alpha > 0.05 (CPURenderer.cpp:32)
     // volume
     uint8_t *d_vol_linear = nullptr;  // always kept: source of every layout, of vr5_get_volume and of the min/max builder

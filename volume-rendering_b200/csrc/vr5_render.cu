@@ -335,7 +335,8 @@ extern "C" int vr5_set_transfer_fn(vr5_renderer *r, const float *tf, const uint3
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     r->have_tf = true;
     r->tf_can_shade = false;  // CPURenderer.cpp:32: only entries with alpha > 0.05 ever reach Raycaster::shade
-    for (int i = 0; i < VR5_TF_SIZE; i++) r->tf_can_shade |= tf[4 * i + 3] > 0.05f;
+    r->tf_opaque = false;         // an entry that can end a ray on its own makes neighbouring rays end at different depths
+    for (int i = 0; i < VR5_TF_SIZE; i++) { r->tf_can_shade |= tf[4 * i + 3] > 0.05f; r->tf_opaque |= tf[4 * i + 3] >= 0.999f; }
     return 0;
 }
 
@@ -704,6 +705,7 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     a->tiles_x = (a->width + kTileW - 1) / kTileW;
     const uint32_t strips = (a->height + kTileH - 1) / kTileH;
     a->tile_rows_local = (uint32_t)r->rank < strips ? (strips - r->rank + r->world - 1) / r->world : 0;
+    a->cta_fetch = (!r->tf_opaque && !getenv("VR5_WARP_FETCH")) ? 1 : 0;
     a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
     const uint32_t groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
     a->n_queue = (a->groups_x * groups_y) << (kGroupLog2X + kGroupLog2Y);
