@@ -96,7 +96,9 @@ int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes);
 int vr5_set_sampler(vr5_renderer *r, int sampler);
 int vr5_get_sampler(const vr5_renderer *r);
 /* Memory path the LAST launch actually took: the VR5_SAMPLER_* id of the kernel variant (a window sampler renders a
- * frame through the clamped texture path when the frame's step could leave the guard margin), -1 before any launch. */
+ * frame through the clamped texture path when the frame's step could leave the guard margin; ids 7..9 are the
+ * power-of-two specialisations of 4..6; VR5_SAMPLER_TRILINEAR + 1 is the trilinear march with unclamped 32-bit record
+ * addressing, VR5_SAMPLER_TRILINEAR itself the clamped one), -1 before any launch. */
 int vr5_last_variant(const vr5_renderer *r);
 
 /* ---- the hot path ----------------------------------------------------------------------------------------- */

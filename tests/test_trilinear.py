@@ -3,6 +3,9 @@
 The CPU side is oracle_port.c's trilinear section ("parity unpinned": GPURenderer4 cannot be built with CUDA 12 and its
 filtering runs in the texture unit's fixed point). The CUDA policy VR5_SAMPLER_TRILINEAR performs the same fp32 operations
 in the same order and is held to bit equality with that restatement."""
+import os
+import subprocess
+
 import numpy as np
 import pytest
 
@@ -33,9 +36,25 @@ def test_oracle_trilinear_is_smooth_where_nearest_steps(port, bucky, golden):
     assert 0 < d.max() and d.mean() < 12
 
 
+def test_division_by_255_identity(tmp_path):
+    """vr5_tri.cuh computes sample / 255 as two FMAs around a multiplication by RN(1/255). The identity with the IEEE
+    division holds for every float in [0, 255] (tools/check_div255.c without an argument checks all 1.13e9 of them); here a
+    strided sample of them."""
+    exe = tmp_path / "check_div255"
+    src = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "check_div255.c")
+    subprocess.run(["gcc", "-O2", "-mfma", "-ffp-contract=off", src, "-o", str(exe), "-lm"], check=True)
+    out = subprocess.run([str(exe), "997"], check=True, capture_output=True, text=True).stdout
+    assert "0 mismatches" in out, out
+
+
 @pytest.mark.gpu
+@pytest.mark.parametrize("clamped", [False, True])
 @pytest.mark.parametrize("name", ["bucky_ortho_0_0_0", "bucky_persp_-45_-45_0", "synthA64_default_persp"])
-def test_gpu_trilinear_matches_restated_oracle(name, golden, port, volumes, R):
+def test_gpu_trilinear_matches_restated_oracle(name, clamped, golden, port, volumes, R, monkeypatch):
+    """Both marches - unclamped 32-bit record addressing (cubic volumes whose step stays inside the guard cells; variant 17)
+    and the clamped one (variant 16, forced here through its knob) - against the restatement, bit for bit."""
+    if clamped:
+        monkeypatch.setenv("VR5_TRI_CLAMPED", "1")
     case = next(c for c in golden["cases"] if c["name"] == name)
     sc = golden_scene(port, case, volumes(case["volume"]))
     scene, params = product_scene(R, sc)
@@ -46,7 +65,7 @@ def test_gpu_trilinear_matches_restated_oracle(name, golden, port, volumes, R):
         frame = gpu.render_volume(params)
         want, cnt = port.render(sc, trilinear=True)
         assert_parity(frame, want, exact=True, what=name)
-        assert gpu.last_variant() == 16
+        assert gpu.last_variant() == (16 if clamped else 17)
         assert gpu.count(params) == cnt
     finally:
         gpu.close()

@@ -29,7 +29,9 @@ struct vr5_renderer {
     int last_variant = -1;  // SAMPLER template id of the last cast_kernel launch
     uint8_t *d_vol_brick = nullptr;
     uint8_t *d_vol_padded = nullptr;  // (nx+1)(ny+1)(nz+1), edge replicated: unclamped LDG path
-    uint8_t *d_cells = nullptr;       // trilinear policy: 8-byte cell records, (nx+1)(ny+1)(nz+1) of them (vr5_tri.cuh)
+    uint8_t *d_cells = nullptr;       // trilinear policy: 8-byte cell records, (n+1+2G) per axis (vr5_tri.cuh)
+    uint64_t cells_bytes = 0;
+    int tri_fast = 0;                 // last trilinear launch used the unclamped 32-bit-address march
     uint8_t *d_vol_window = nullptr;  // window layout (fetch mode 4), NULL when the volume does not fit one 4-GiB window
     uint32_t win_hi = 0, win_sx = 0, win_sxy = 0;
     float win_mx = 0, win_my = 0, win_mz = 0;
@@ -70,7 +72,7 @@ struct vr5_renderer {
     size_t peer_frame_stride = 0;
     uint32_t peer_released_slot[16] = {0};  // owner, host side: releases per slot so far
     // bookkeeping
-    int ctas_per_sm[256] = {0};  // occupancy cache per kernel variant
+    int ctas_per_sm[512] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
     void *d_flush = nullptr;
     size_t flush_bytes = 0;

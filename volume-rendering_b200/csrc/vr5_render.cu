@@ -89,13 +89,13 @@ __global__ void p2_layout_kernel(const uint8_t *__restrict__ lin, uint8_t *__res
     }
 }
 
-// linear -> trilinear cells (vr5_tri.cuh): record (jx, jy, jz) = the eight voxels around cell i0 = j - 1, clamped to the grid;
-// byte b of the 8-byte record is the neighbour with offsets (b & 1, (b >> 1) & 1, b >> 2)
+// linear -> trilinear cells (vr5_tri.cuh): record (jx, jy, jz) = the eight voxels around cell i0 = j - 1 - G, clamped to the
+// grid (G guard cells per side); byte b of the 8-byte record is the neighbour with offsets (b & 1, (b >> 1) & 1, b >> 2)
 __global__ void cell_layout_kernel(const uint8_t *__restrict__ lin, uint2 *__restrict__ cells, uint32_t nx, uint32_t ny, uint32_t nz) {
-    const uint32_t cx = nx + 1, cy = ny + 1, cz = nz + 1;
+    const uint32_t cx = nx + 1 + 2 * kTriGuard, cy = ny + 1 + 2 * kTriGuard, cz = nz + 1 + 2 * kTriGuard;
     const uint64_t n = (uint64_t)cx * cy * cz;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-        const int x0 = (int)(i % cx) - 1, y0 = (int)((i / cx) % cy) - 1, z0 = (int)(i / ((uint64_t)cx * cy)) - 1;
+        const int x0 = (int)(i % cx) - 1 - kTriGuard, y0 = (int)((i / cx) % cy) - 1 - kTriGuard, z0 = (int)(i / ((uint64_t)cx * cy)) - 1 - kTriGuard;
         uint32_t w[2] = {0u, 0u};
 #pragma unroll
         for (int b = 0; b < 8; b++) {
@@ -492,9 +492,20 @@ static int build_layout(vr5_renderer *r) {
     free_layouts(r);
     if (!r->d_vol_linear) return 0;
     if (r->sampler == VR5_SAMPLER_TRILINEAR) {
-        const uint64_t bytes = (uint64_t)(r->nx + 1) * (r->ny + 1) * (r->nz + 1) * 8u;
-        cudaError_t e = cudaMalloc(&r->d_cells, bytes);
-        if (e != cudaSuccess) { r->d_cells = nullptr; vr5_fail(r, "cudaMalloc trilinear cells (8 bytes per voxel)", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
+        const uint64_t bytes = (uint64_t)(r->nx + 1 + 2 * kTriGuard) * (r->ny + 1 + 2 * kTriGuard) * (r->nz + 1 + 2 * kTriGuard) * 8u;
+        // the unclamped march wants the array inside one 4-GiB address window: an allocation that straddles one is retried
+        uint8_t *held[4] = {nullptr, nullptr, nullptr, nullptr};
+        cudaError_t e = cudaSuccess;
+        for (int tries = 0; tries < 4; tries++) {
+            e = cudaMalloc(&r->d_cells, bytes);
+            if (e != cudaSuccess) { r->d_cells = nullptr; break; }
+            const uint64_t a0 = (uint64_t)(uintptr_t)r->d_cells;
+            if (bytes >= (1ull << 32) || (a0 >> 32) == ((a0 + bytes - 1) >> 32) || tries == 3) break;
+            held[tries] = r->d_cells; r->d_cells = nullptr;
+        }
+        for (uint8_t *h : held) if (h) cudaFree(h);
+        if (!r->d_cells) { vr5_fail(r, "cudaMalloc trilinear cells (8 bytes per voxel)", e, __FILE__, __LINE__); cudaGetLastError(); return 1; }
+        r->cells_bytes = bytes;
         cell_layout_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, reinterpret_cast<uint2 *>(r->d_cells), r->nx, r->ny, r->nz);
         r->launches++;
         VR5_CUDA(r, cudaGetLastError());
@@ -780,23 +791,35 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
     if (r->sampler == VR5_SAMPLER_TRILINEAR) {  // GPURenderer4 semantics in software fp32 (vr5_tri.cuh)
         TriArgs t;
         t.cells = reinterpret_cast<const uint2 *>(r->d_cells);
-        t.cx = r->nx + 1; t.cy = r->ny + 1;
-        t.nfx = (float)r->nx; t.nfy = (float)r->ny; t.nfz = (float)r->nz;
-        t.nx = r->nx; t.ny = r->ny; t.nz = r->nz;
-        int &per_sm = r->ctas_per_sm[count ? 254 : 255];
+        t.cx = r->nx + 1 + 2 * kTriGuard; t.cy = r->ny + 1 + 2 * kTriGuard;
+        t.hfx = a.hx; t.hfy = a.hy; t.hfz = a.hz;
+        t.jx1 = r->nx + 2 * kTriGuard; t.jy1 = r->ny + 2 * kTriGuard; t.jz1 = r->nz + 2 * kTriGuard;
+        // unclamped 32-bit addressing: record j = b - (bits(magic) - 1 - G) per axis, byte address = base + 8 * rec
+        const uint64_t base = (uint64_t)(uintptr_t)r->d_cells;
+        const bool one_window = r->cells_bytes < (1ull << 32) && (base >> 32) == ((base + r->cells_bytes - 1) >> 32);
+        const uint32_t kb = kTriMagicBits - 1u - (uint32_t)kTriGuard;
+        t.hi = (uint32_t)(base >> 32);
+        t.s1 = 8u * t.cx; t.s2 = 8u * t.cx * t.cy;                       // mod 2^32 like every term of the address sum
+        t.c0 = (uint32_t)base - kb * (t.s2 + t.s1 + 8u);
+        // one march step may leave the cube by step * |d| * n/2 cells per axis (+1 for the cell's far corner, +1 rounding)
+        const bool fast = one_window && cube && !count && !getenv("VR5_TRI_CLAMPED") && reach_ok(a, (float)(kTriGuard - 2));
+        // variants: instrumented (clamped, shading code present), and {clamped, unclamped} x {shading code, none}
+        const int v = count ? 0 : 1 + (fast ? 2 : 0) + (shade ? 1 : 0);
+        void (*const kernels[5])(const KArgs, const TriArgs) = {tri_kernel<true, false, true>, tri_kernel<false, false, false>, tri_kernel<false, false, true>,
+                                                                tri_kernel<false, true, false>, tri_kernel<false, true, true>};
+        int &per_sm = r->ctas_per_sm[507 + v];
         if (per_sm == 0) {
-            e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tri_kernel<true>, kCtaThreads, 0)
-                      : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tri_kernel<false>, kCtaThreads, 0);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernels[v], kCtaThreads, 0);
             if (e != cudaSuccess || per_sm < 1) per_sm = 1;
         }
         uint32_t grid = (uint32_t)(r->num_sms * per_sm);
         const uint32_t needed = (a.n_queue + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
         if (grid > needed) grid = needed ? needed : 1;
-        if (count) tri_kernel<true><<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
-        else tri_kernel<false><<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
+        kernels[v]<<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
+        r->tri_fast = fast ? 1 : 0;
         r->last_grid = grid;
         r->launches++;
-        r->last_variant = VR5_SAMPLER_TRILINEAR;
+        r->last_variant = VR5_SAMPLER_TRILINEAR + (fast ? 1 : 0);
         e = cudaGetLastError();
         if (e != cudaSuccess) { vr5_fail(r, "tri_kernel launch", e, __FILE__, __LINE__); return 1; }
         return 0;

@@ -11,73 +11,107 @@
 
 namespace vr5 {
 
+constexpr int kTriGuard = 8;  // guard cells on every side of the record array (unclamped march: host check tri_reach_ok)
+constexpr float kTriMagic = 12582912.0f;      // 1.5 * 2^23: floor(t) == bits(RD(t + magic)) - bits(magic) for |t| < 2^22
+constexpr uint32_t kTriMagicBits = 0x4B400000u;
+
 struct TriArgs {
-    const uint2 *cells;      // (nx+1)(ny+1)(nz+1) records, x fastest; record j holds cell i0 = j - 1
-    uint32_t cx, cy;         // records per row / rows per slice (nx + 1, ny + 1)
-    float nfx, nfy, nfz;     // dims as float
-    uint32_t nx, ny, nz;
+    const uint2 *cells;      // (nx+1+2G)(ny+1+2G)(nz+1+2G) records, x fastest; record j holds cell i0 = j - 1 - G (clamped)
+    uint32_t cx, cy;         // records per row / rows per slice
+    float hfx, hfy, hfz;     // dims * 0.5f: ((p + 1) * 0.5f) * n == (p + 1) * (0.5f * n) exactly (power-of-two scaling)
+    uint32_t jx1, jy1, jz1;  // last record index per axis (n + 2G)
+    // unclamped march (FAST): the array lies inside one 4-GiB address window and the low 32 address bits of the record of a
+    // point are bz*s2 + by*s1 + bx*8 + c0 (mod 2^32), b = bit pattern of RD(t + magic) per axis
+    uint32_t hi, c0, s1, s2;
 };
 
+// the march loop's uniform operands. With VR5_TRI_PIN they are read once per thread through a volatile shared copy, which
+// pins them in registers; otherwise ptxas re-loads them from the constant bank (LDCU) in every iteration.
+#ifndef VR5_TRI_PIN
+#define VR5_TRI_PIN 1
+#endif
+struct TriRegs { float step, threshold, hfx, hfy, hfz; uint32_t s1, s2, c0, hi, pair_c; };
+
 // one axis: texel position t = ((p + 1) * 0.5) * n - 0.5, cell floor(t), weight t - floor(t). floor() comes from an add
-// rounded toward -inf against 1.5 * 2^23 (exact for |t| < 2^22), whose bit pattern also carries the integer.
-__device__ __forceinline__ void tri_axis(float p, float nf, uint32_t n, uint32_t &j, float &w) {
-    const float t = fsub(fmul(fmul(fadd(p, 1.0f), 0.5f), nf), 0.5f);
-    const float magic = 12582912.0f;
-    const float tm = __fadd_rd(t, magic);
-    const float fl = fsub(tm, magic);  // exact
-    w = fsub(t, fl);
-    const int i0 = (int)(__float_as_uint(tm) - 0x4B400000u);  // floor(t) as an integer
-    j = (uint32_t)min(max(i0 + 1, 0), (int)n);                 // record index; clamps both neighbours like the oracle
+// rounded toward -inf against 1.5 * 2^23, whose bit pattern also carries the integer. Returns the biased bits.
+__device__ __forceinline__ uint32_t tri_axis(float p, float hf, float &w) {
+    const float t = fsub(fmul(fadd(p, 1.0f), hf), 0.5f);
+    const float tm = __fadd_rd(t, kTriMagic);
+    w = fsub(t, fsub(tm, kTriMagic));  // tm - magic is exact
+    asm volatile("" : "+f"(w));        // keep the weight in its register: ptxas otherwise recomputes the whole axis after the loop body
+    return __float_as_uint(tm);
 }
 
-__device__ __forceinline__ float byte_to_float(uint32_t word, int i) {
-    return fsub(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u + (uint32_t)i)), 8388608.0f);
+// byte i of a record word as the float 2^23 + byte (one PRMT, no conversion unit: I2F runs at 1/8 rate)
+__device__ __forceinline__ float byte_biased(uint32_t word, int i) {
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u + (uint32_t)i));
 }
 
 __device__ __forceinline__ float lerp_rn(float a, float b, float w) { return fadd(a, fmul(w, fsub(b, a))); }
+// a + w * (b - a) with a and b still biased by 2^23: the difference of the biased values IS b - a (exact, both in
+// [2^23, 2^23 + 255]), so only a needs the exact un-biasing subtraction
+__device__ __forceinline__ float lerp_biased(float ab, float bb, float w) { return fadd(fsub(ab, 8388608.0f), fmul(w, fsub(bb, ab))); }
+
+// x / 255 correctly rounded without the division sequence: q0 = RN(x * r), rem = x - q0 * 255 (exact in an FMA), q = RN(q0 +
+// rem * r) with r = RN(1 / 255). Equal to __fdiv_rn(x, 255.0f) for EVERY float in [0, 255] - checked exhaustively over all
+// 1 132 396 545 bit patterns (tools/check_div255.c; tests/test_trilinear.py runs a strided sample of it).
+__device__ __forceinline__ float div255(float x) {
+    const float r = 0x1.010102p-8f;
+    const float q0 = fmul(x, r);
+    return __fmaf_rn(__fmaf_rn(-q0, 255.0f, x), r, q0);
+}
 
 // request the cell record of a point (the load) and keep its three weights
 struct TriTap { uint2 c; float wx, wy, wz; };
-__device__ __forceinline__ TriTap tri_request(const TriArgs &t, float px, float py, float pz) {
-    uint32_t jx, jy, jz;
+template <bool FAST>
+__device__ __forceinline__ TriTap tri_request(const TriArgs &t, const TriRegs &g, float px, float py, float pz) {
     TriTap tap;
-    tri_axis(px, t.nfx, t.nx, jx, tap.wx);
-    tri_axis(py, t.nfy, t.ny, jy, tap.wy);
-    tri_axis(pz, t.nfz, t.nz, jz, tap.wz);
-    const uint64_t rec = ((uint64_t)jz * t.cy + jy) * t.cx + jx;
-    tap.c = __ldg(t.cells + rec);
+    const uint32_t bx = tri_axis(px, g.hfx, tap.wx), by = tri_axis(py, g.hfy, tap.wy), bz = tri_axis(pz, g.hfz, tap.wz);
+    if (FAST) {
+        uint32_t lo;
+        asm("{\n\t.reg .u32 t;\n\tmad.lo.u32 t, %3, %5, %6;\n\tmad.lo.u32 t, %2, %4, t;\n\tshl.b32 %0, %1, 3;\n\tadd.u32 %0, %0, t;\n\t}"
+            : "=r"(lo) : "r"(bx), "r"(by), "r"(bz), "r"(g.s1), "r"(g.s2), "r"(g.c0));
+        asm("{\n\t.reg .u64 p;\n\tmov.b64 p, {%2, %3};\n\tld.global.nc.v2.u32 {%0, %1}, [p];\n\t}" : "=r"(tap.c.x), "=r"(tap.c.y) : "r"(lo), "r"(g.hi));
+    } else {  // record index clamped: the guard records already hold the clamped neighbours, like the checker's index clamp
+        const int bias = (int)kTriMagicBits - 1 - kTriGuard;
+        const uint32_t jx = (uint32_t)min(max((int)bx - bias, 0), (int)t.jx1);
+        const uint32_t jy = (uint32_t)min(max((int)by - bias, 0), (int)t.jy1);
+        const uint32_t jz = (uint32_t)min(max((int)bz - bias, 0), (int)t.jz1);
+        tap.c = __ldg(t.cells + (((uint64_t)jz * t.cy + jy) * t.cx + jx));
+    }
     return tap;
 }
 
-// oracle fetch_trilinear: lerp x, then y, then z on the raw byte values, result / 255
+// checker's fetch_trilinear: lerp x, then y, then z on the raw byte values, result / 255
 __device__ __forceinline__ float tri_resolve(const TriTap &tap) {
     const uint2 c = tap.c;
     const float wx = tap.wx, wy = tap.wy, wz = tap.wz;
-    // byte -> float without the conversion unit (I2F runs at 1/8 rate): drop the byte into the mantissa of 2^23 with one
-    // PRMT, subtract 2^23 (exact)
-    const float v000 = byte_to_float(c.x, 0), v100 = byte_to_float(c.x, 1), v010 = byte_to_float(c.x, 2), v110 = byte_to_float(c.x, 3);
-    const float v001 = byte_to_float(c.y, 0), v101 = byte_to_float(c.y, 1), v011 = byte_to_float(c.y, 2), v111 = byte_to_float(c.y, 3);
-    const float c00 = lerp_rn(v000, v100, wx), c10 = lerp_rn(v010, v110, wx);
-    const float c01 = lerp_rn(v001, v101, wx), c11 = lerp_rn(v011, v111, wx);
+    const float c00 = lerp_biased(byte_biased(c.x, 0), byte_biased(c.x, 1), wx), c10 = lerp_biased(byte_biased(c.x, 2), byte_biased(c.x, 3), wx);
+    const float c01 = lerp_biased(byte_biased(c.y, 0), byte_biased(c.y, 1), wx), c11 = lerp_biased(byte_biased(c.y, 2), byte_biased(c.y, 3), wx);
     const float c0 = lerp_rn(c00, c10, wy), c1 = lerp_rn(c01, c11, wy);
-    return fdiv(lerp_rn(c0, c1, wz), 255.0f);
+    return div255(lerp_rn(c0, c1, wz));
 }
 
-__device__ __forceinline__ float tri_fetch(const TriArgs &t, float px, float py, float pz) { return tri_resolve(tri_request(t, px, py, pz)); }
+__device__ __forceinline__ float tri_fetch(const TriArgs &t, const TriRegs &g, float px, float py, float pz) { return tri_resolve(tri_request<false>(t, g, px, py, pz)); }
 
-// oracle classify_linear: 128-entry table, position s * 128 - 0.5, clamp, per-channel lerp
-__device__ __forceinline__ float4 tri_classify(const float4 *s_tf, float s) {
+// checker's classify_linear: 128-entry table, position s * 128 - 0.5, clamp, per-channel lerp a + w * (b - a).
+// The shared table holds, for every f = floor(position) in [-1, 127], the pair (tf[clamp(f)], tf[clamp(f+1)] - tf[clamp(f)]):
+// no index clamps and no subtraction in the loop (the difference is the same RN subtraction, done once per CTA).
+constexpr int kTriPairs = 129;
+// pair_c = shared address of the table - ((bits(magic) - 1) << 5) (mod 2^32): the entry address is one shift-add of the bits
+__device__ __forceinline__ float4 tri_classify(uint32_t pair_c, float s) {
     const float t = fsub(fmul(s, 128.0f), 0.5f);
-    const float fl = floorf(t);
-    const float w = fsub(t, fl);
-    const int f = (int)fl;
-    const int j0 = min(max(f, 0), 127), j1 = min(max(f + 1, 0), 127);
-    const float4 a = s_tf[j0], b = s_tf[j1];
-    return make_float4(lerp_rn(a.x, b.x, w), lerp_rn(a.y, b.y, w), lerp_rn(a.z, b.z, w), lerp_rn(a.w, b.w, w));
+    const float tm = __fadd_rd(t, kTriMagic);
+    const float w = fsub(t, fsub(tm, kTriMagic));
+    const uint32_t addr = pair_c + (__float_as_uint(tm) << 5);
+    float4 a, d;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(addr));
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr));
+    return make_float4(fadd(a.x, fmul(w, d.x)), fadd(a.y, fmul(w, d.y)), fadd(a.z, fmul(w, d.z)), fadd(a.w, fmul(w, d.w)));
 }
 
-template <bool COUNT>
-__device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &t, const float4 *s_tf, const uint32_t *esl_bits, int col, int row,
+template <bool COUNT, bool FAST, bool SHADE>
+__device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, int col, int row,
                                                  Counters &cnt) {
     // View::get_ray, Raycaster::intersect and the leading empty-space loop are those of the nearest path (vr5_cast.cuh)
     const float cx = (float)(col - a.half_w), cy = (float)(row - a.half_h);
@@ -105,7 +139,7 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
     }
     if (COUNT) cnt.rays_hit++;
     float px = fadd(ox, fmul(dx, k)), py = fadd(oy, fmul(dy, k)), pz = fadd(oz, fmul(dz, k));
-    const float step = a.step;
+    const float step = g.step;
     if (a.esl) {
         while (k <= k_far) {
             uint32_t bx = div_block(a, world_to_voxel(px, a.hx, a.nx1));
@@ -135,29 +169,32 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
     if (!(k <= k_far)) return 0u;
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
     // software pipelined like the nearest path: the cell of sample i + 1 is requested before sample i is interpolated and
-    // composited (speculative past k_far: the record index is clamped, so the load is always in bounds)
-    TriTap tap = tri_request(t, px, py, pz);
+    // composited (speculative past k_far: the record index is clamped, or - FAST - the host has checked that one step stays
+    // inside the guard cells, so the load is always in bounds)
+    TriTap tap = tri_request<false>(t, g, px, py, pz);
     while (k <= k_far) {  // GPURenderer4.cu:75-86
         const float kn = fadd(k, step);
         const float nx = fadd(ox, fmul(dx, kn)), ny = fadd(oy, fmul(dy, kn)), nz = fadd(oz, fmul(dz, kn));
-        const TriTap next = tri_request(t, nx, ny, nz);
+        const TriTap next = tri_request<FAST>(t, g, nx, ny, nz);
         const float s = tri_resolve(tap);
-        float4 c = tri_classify(s_tf, s);
+        float4 c = tri_classify(g.pair_c, s);
         if (COUNT) cnt.samples++;
-        if (c.w > a.shade_alpha) {  // GPURenderer4.cu:78 guard, :41-51 shade_texture
+        // SHADE=false: the host has seen that no TF entry exceeds the guard's alpha (an interpolated alpha never exceeds both
+        // of its entries) or that light_kd <= 0.01
+        if (SHADE && c.w > a.shade_alpha) {  // GPURenderer4.cu:78 guard, :41-51 shade_texture
             const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
             const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
             const float inv = fdiv(1.0f, __fsqrt_rn(len2));
             const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
             const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
             const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
-            const float diffuse = fmul(fsub(tri_fetch(t, qx, qy, qz), s), a.kd);
+            const float diffuse = fmul(fsub(tri_fetch(t, g, qx, qy, qz), s), a.kd);
             c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
             if (COUNT) cnt.shaded++;
         }
         const float tr = fsub(1.0f, aa);
         ar = fadd(ar, fmul(c.x, tr)); ag = fadd(ag, fmul(c.y, tr)); ab = fadd(ab, fmul(c.z, tr)); aa = fadd(aa, fmul(c.w, tr));
-        if (aa > a.threshold) break;
+        if (aa > g.threshold) break;
         k = kn; px = nx; py = ny; pz = nz; tap = next;
     }
     return trunc_clamp(fmul(ar, 256.0f), 255u) | (trunc_clamp(fmul(ag, 256.0f), 255u) << 8) |
@@ -165,14 +202,28 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
 }
 
 // same persistent-warp / tile-queue skeleton as cast_kernel
-template <bool COUNT>
-__global__ void __launch_bounds__(kCtaThreads) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
-    __shared__ float4 s_tf[128];
+template <bool COUNT, bool FAST, bool SHADE>
+__global__ void __launch_bounds__(kCtaThreads, SHADE ? 0 : 6) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
+    __shared__ float4 s_pair[kTriPairs][2];
     __shared__ uint32_t s_esl[1024];
-    for (int i = threadIdx.x; i < 128; i += kCtaThreads) s_tf[i] = a.tf[i];
+    for (int i = threadIdx.x; i < kTriPairs; i += kCtaThreads) {
+        const float4 lo = a.tf[min(max(i - 1, 0), 127)], hi = a.tf[min(i, 127)];
+        s_pair[i][0] = lo;
+        s_pair[i][1] = make_float4(fsub(hi.x, lo.x), fsub(hi.y, lo.y), fsub(hi.z, lo.z), fsub(hi.w, lo.w));
+    }
     for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
     __syncthreads();
     const int lane = threadIdx.x & 31;
+    const uint32_t pair_c = (uint32_t)__cvta_generic_to_shared(&s_pair[0][0]) - ((kTriMagicBits - 1u) << 5);
+#if VR5_TRI_PIN
+    __shared__ TriRegs s_regs;
+    if (threadIdx.x == 0) s_regs = TriRegs{a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c};
+    __syncthreads();
+    const volatile TriRegs *vr = &s_regs;
+    const TriRegs g = {vr->step, vr->threshold, vr->hfx, vr->hfy, vr->hfz, vr->s1, vr->s2, vr->c0, vr->hi, vr->pair_c};
+#else
+    const TriRegs g = {a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c};
+#endif
     Counters cnt = {0, 0, 0, 0, 0};
     for (;;) {
         unsigned q = 0;
@@ -186,7 +237,7 @@ __global__ void __launch_bounds__(kCtaThreads) tri_kernel(const __grid_constant_
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
         if (col < a.width && row < a.height) {
-            const uint32_t rgba = cast_ray_tri<COUNT>(a, t, s_tf, s_esl, col, row, cnt);
+            const uint32_t rgba = cast_ray_tri<COUNT, FAST, SHADE>(a, t, g, s_esl, col, row, cnt);
             if (!COUNT) {
                 const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
                 reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;
