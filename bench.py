@@ -429,7 +429,7 @@ def run_b200_arm(args, wl):
                        "l2": "no flush in the timed loop: per frame the kernel reads the %.0f MB volume and writes the %.1f MB frame (L2 is 126 MB); "
                              "the flushed per-kernel time is reported in roofline.kernel_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_src, "kernel": ("vr5::tri_kernel" if args.sampler == "trilinear" else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant())),
+                         "peak_source": peak_src, "kernel": ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler == "trilinear" else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant())),
                          "bytes_per_sample": voxel_bytes, "kernel_ms": float(k_ms.mean()),
                          "kernel_ms_l2_flushed": float(k_ms_flushed.mean()), "algorithmic_bytes_per_launch": alg_bytes,
                          "note": ("trilinear policy (GPURenderer4 semantics, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear" else
