@@ -22,9 +22,18 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly one JSON line: NCCL's version banner (NCCL_DEBUG=VERSION/INFO prints to stdout) would break that
+# stdout carries exactly one JSON line. Libraries write there too (NCCL's version banner at communicator creation, the
+# reference's Logger), so file descriptor 1 is pointed at stderr for the life of the process and the line goes to the saved one.
 if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE") and not os.environ.get("NCCL_DEBUG_FILE"):
     os.environ["NCCL_DEBUG"] = "WARN"
+sys.stdout.flush()
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
 
 WORKLOADS = {  # BASELINE.json configs[1..4]
     "c2": dict(kind=0, n=256, seed=1, tf="semi", w=1920, h=1080, name="synthA 256^3 uint8, semi TF, 1920x1080, 360-frame orbit"),
@@ -218,7 +227,7 @@ def run_reference_arm(args, wl):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---- this repo's arm ---------------------------------------------------------------------------------------------------
@@ -444,7 +453,7 @@ def run_b200_arm(args, wl):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args, wl)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     gpu.close()
     if world > 1:
         dist.destroy_process_group()
