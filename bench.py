@@ -285,6 +285,41 @@ def run_b200_arm(args, wl):
             gpu.peer_open(box[0], PEER_SLOTS)
         dist.barrier()
     seq = [0]
+    # end-to-end leg at N > 1: "host" = every rank copies its own strips into a frame ring in shared HOST memory over its
+    # own PCIe link (csrc/vr5_hostring.cu); "peer" = rank 0 copies the gathered frame from its HBM (one link for all)
+    e2e_gather = args.e2e_gather if (world > 1 and gather == "peer") else "same"
+    hseq, hrel, ring_mem, ring_name = [0], [0], None, None
+    hprof = [0.0, 0.0]
+    # The consumer learns of a delivery through host memory, later than a stream would, and a frame is only delivered after
+    # kernel + copy + flag: it trails the producers by RING_LAG frames (measured at N=8: lag 3 -> 6 300 FPS, 4 -> 8 100,
+    # >= 7 -> the device rate), in a ring of 3 x lanes slots (producer of frame j needs frame j - slots released).
+    RING_SLOTS = 3 * max(1, args.overlap)
+    RING_LAG = RING_SLOTS - max(1, args.overlap) - 1
+    if os.environ.get("VR5_RING_SLOTS"):   # experiment knobs
+        RING_SLOTS = int(os.environ["VR5_RING_SLOTS"])
+    if os.environ.get("VR5_RING_LAG"):
+        RING_LAG = int(os.environ["VR5_RING_LAG"])
+    if e2e_gather == "host":     # the ring must fit the node's shared memory, else fall back to rank 0's copy
+        fits = [False]
+        if rank == 0:
+            try:
+                st = os.statvfs("/dev/shm")
+                fits[0] = st.f_bavail * st.f_frsize > 1.25 * R.hostring_bytes(w, h, RING_SLOTS)
+            except OSError:
+                pass
+        dist.broadcast_object_list(fits, src=0)
+        if not fits[0]:
+            e2e_gather = "peer"
+    if e2e_gather == "host":
+        nbytes = R.hostring_bytes(w, h, RING_SLOTS)
+        box = ["vr5_ring_%d_%d" % (os.getpid(), int(time.time())) if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        ring_name = box[0]
+        if rank == 0:
+            ring_mem = R.ring_memory(ring_name, nbytes, create=True)
+        dist.barrier()
+        if rank != 0:
+            ring_mem = R.ring_memory(ring_name, nbytes, create=False)
 
     L = R.lib()
     rows_padded = max(L.vr5_strip_rows(h, r, world) for r in range(world))
@@ -325,6 +360,18 @@ def run_b200_arm(args, wl):
             seq[0] += 1
             if i >= lanes - 1:
                 gpu.sync_lane((i - (lanes - 1)) % lanes)
+        elif e2e_gather == "host":
+            j = hseq[0]
+            ta = time.perf_counter()
+            gpu.hostring_render(p, j)          # kernel + strided D2H of this rank's strips into the shared host frame
+            tb = time.perf_counter()
+            hseq[0] += 1
+            if rank == 0 and j >= RING_LAG:    # the consumer receives every frame, in order, RING_LAG frames behind
+                gpu.hostring_wait(hrel[0])     # all ranks' strips of that frame are in host memory
+                gpu.hostring_release(hrel[0])
+                hrel[0] += 1
+            tc = time.perf_counter()
+            hprof[0] += tb - ta; hprof[1] += tc - tb
         elif gather == "peer":
             gpu.peer_render(p, i)
             if rank == 0:
@@ -394,14 +441,40 @@ def run_b200_arm(args, wl):
     clocks.stop()
 
     # -- end to end: host buffers, blocking call per frame, wall clock, max over ranks --------------------------------
+    def drain_host():
+        while rank == 0 and hrel[0] < hseq[0]:   # the last lanes - 1 frames
+            gpu.hostring_wait(hrel[0])
+            gpu.hostring_release(hrel[0])
+            hrel[0] += 1
+
+    if e2e_gather == "host":
+        gpu.sync()
+        gpu.set_partition(rank, world, True)     # packed strips for the strided copy
+        if rank == 0:
+            gpu.hostring_attach(ring_mem, RING_SLOTS, init=True)    # clears the header before anyone else looks at it
+        dist.barrier()
+        if rank != 0:
+            gpu.hostring_attach(ring_mem, RING_SLOTS, init=False)
+        dist.barrier()
     for p in warm[:3]:
         step_e2e(p)
+    drain_host()
     barrier()
     t0 = time.perf_counter()
     for p in frames:
         step_e2e(p)
+    drain_host()
     barrier()
     e2e_s = time.perf_counter() - t0
+    if os.environ.get("VR5_BENCH_DEBUG"):
+        print("rank %d: e2e %.1f ms, in render calls %.1f ms, in wait/release %.1f ms" % (rank, e2e_s * 1e3, hprof[0] * 1e3, hprof[1] * 1e3), file=sys.stderr)
+    if e2e_gather == "host":
+        gpu.hostring_detach()
+        gpu.set_partition(rank, world, False)
+        ring_mem.close()
+        dist.barrier()
+        if rank == 0:
+            R.ring_memory_unlink(ring_name)
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -444,7 +517,9 @@ def run_b200_arm(args, wl):
                          "note": ("trilinear policy (GPURenderer4 semantics, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear" else
                                   "parity mode fetches 1 B per sample; the kernel is bound by the fp32 pipe and issue slots, not by HBM (DESIGN.md)")},
             "e2e": {"value": samples_total / e2e_s / 1e9, "unit": UNIT, "fps": args.steps / e2e_s, "h2d_bytes_per_step": C.sizeof(R.Params),
-                    "d2h_bytes_per_step": w * h * 4},
+                    "d2h_bytes_per_step": w * h * 4,
+                    "path": {"host": "every rank copies its strips into a frame ring in shared host memory over its own PCIe link (vr5_hostring_*)",
+                             "peer": "rank 0 copies the frame gathered in its HBM (vr5_peer_read)", "same": "kernel + D2H of the frame on its lane"}[e2e_gather]},
             "gpu_launches": launches, "clocks": clocks.summary(),
         }
     if world > 1:
@@ -488,6 +563,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap", type=int, default=4, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how strips reach rank 0")
+    ap.add_argument("--e2e-gather", default="host", choices=["host", "peer"],
+                    help="N > 1, end-to-end leg: host = every rank copies its strips into a shared host frame ring; peer = rank 0 copies the gathered frame")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

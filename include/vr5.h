@@ -193,6 +193,28 @@ int vr5_peer_sync_frame(vr5_renderer *r, uint64_t seq);
 int vr5_peer_status(vr5_renderer *r);
 void vr5_peer_close(vr5_renderer *r);
 
+/* ---- host frame ring: every rank delivers its strips to HOST memory over its own PCIe link (vr5_hostring.cu) ---- */
+
+/* The reference's renderers 1-2 hand the finished frame to the caller in host memory (VolR.cpp:76-87). With several GPUs,
+ * gathering on one device and copying from there makes that device's PCIe link the limit; here the ring of `slots` frames
+ * lives in host memory visible to all ranks (POSIX shared memory between processes; any memory inside one process). Every
+ * rank renders its strips packed (vr5_set_partition(..., packed = 1)) and copies them straight to their rows of the
+ * frame's slot. Frame seq uses slot seq % slots and lane seq % lanes (slots a multiple of lanes). No device waits for
+ * another one; both hand-shakes (slot released / all strips delivered) are bounded host-side polls of counters in the
+ * ring's header (4 s, then an error). */
+uint64_t vr5_hostring_bytes(uint16_t width, uint16_t height, int slots);   /* header + slots frames; slots 1..16 */
+/* Page-lock `base` for this device (cudaHostRegister; already pinned memory is used as it is) and use it as the ring for the
+ * current window and partition. init = 1 on exactly one rank, before the others attach: clears the header. */
+int vr5_hostring_attach(vr5_renderer *r, void *base, uint64_t bytes, int slots, int init);
+/* any rank: render this rank's strips of frame `seq`, copy them into the ring, signal. Asynchronous on the frame's lane;
+ * blocks the host (bounded) only while frame seq - slots has not been released. */
+int vr5_hostring_render(vr5_renderer *r, const vr5_params *p, uint64_t seq);
+/* consumer: block (bounded) until all `world` ranks delivered frame `seq`; *frame_out = the frame inside the ring, valid
+ * until vr5_hostring_release(seq) */
+int vr5_hostring_wait(vr5_renderer *r, uint64_t seq, const void **frame_out);
+int vr5_hostring_release(vr5_renderer *r, uint64_t seq);
+void vr5_hostring_detach(vr5_renderer *r);
+
 /* ---- synthetic volumes generated on the device (bench inputs) ------------------------------- */
 
 /* kind 0 = synthA (dense Marschner-Lobb-like), 1 = synthB (sparse spheres); integer arithmetic, byte-identical to

@@ -6,7 +6,7 @@ cd "$(dirname "$0")/../volume-rendering_b200/csrc"
 name=$1; shift
 mkdir -p ../build/var/$name.o
 F="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false -ftz=false -prec-div=true -prec-sqrt=true -Xcompiler -fPIC $*"
-for f in vr5_render.cu vr5_synth.cu vr5_prep.cu vr5_peer.cu vr5_scene.cpp vr5_volio.cpp; do nvcc $F -c $f -o ../build/var/$name.o/$f.o & done
+for f in vr5_render.cu vr5_synth.cu vr5_prep.cu vr5_peer.cu vr5_hostring.cu vr5_scene.cpp vr5_volio.cpp; do nvcc $F -c $f -o ../build/var/$name.o/$f.o & done
 wait
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../build/var/$name.so ../build/var/$name.o/*.o -lcudart
 echo built $name

@@ -117,6 +117,12 @@ def lib() -> C.CDLL:
         "vr5_peer_sync_frame": (C.c_int, [vp, C.c_uint64]),
         "vr5_peer_status": (C.c_int, [vp]),
         "vr5_peer_close": (None, [vp]),
+        "vr5_hostring_bytes": (C.c_uint64, [C.c_uint16, C.c_uint16, C.c_int]),
+        "vr5_hostring_attach": (C.c_int, [vp, vp, C.c_uint64, C.c_int, C.c_int]),
+        "vr5_hostring_render": (C.c_int, [vp, C.POINTER(Params), C.c_uint64]),
+        "vr5_hostring_wait": (C.c_int, [vp, C.c_uint64, C.POINTER(vp)]),
+        "vr5_hostring_release": (C.c_int, [vp, C.c_uint64]),
+        "vr5_hostring_detach": (None, [vp]),
         "vr5_synth_volume": (C.c_int, [vp, C.c_int, C.c_uint16, C.c_uint32]),
         "vr5_load_pvm": (C.c_int, [C.c_char_p, C.POINTER(u8p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), f32p]),
         "vr5_load_raw": (C.c_int, [C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(u8p)]),

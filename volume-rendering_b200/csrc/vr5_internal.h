@@ -71,6 +71,10 @@ struct vr5_renderer {
     int peer_slots = 0;
     size_t peer_frame_stride = 0;
     uint32_t peer_released_slot[16] = {0};  // owner, host side: releases per slot so far
+    // host frame ring (vr5_hostring.cu): shared host memory, every rank copies its strips there over its own PCIe link
+    uint8_t *hr_base = nullptr, *hr_dev = nullptr;  // host address / device alias of the page-locked block
+    int hr_slots = 0;
+    bool hr_registered = false;       // this handle page-locked the block (and un-registers it on detach)
     // bookkeeping
     int ctas_per_sm[512] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;

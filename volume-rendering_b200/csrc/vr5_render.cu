@@ -295,6 +295,7 @@ extern "C" void vr5_destroy(vr5_renderer *r) {
     if (!r) return;
     cudaSetDevice(r->device);
     sync_all(r);
+    vr5_hostring_detach(r);
     vr5_peer_close(r);
     free_layouts(r);
     cudaFree(r->d_vol_linear);

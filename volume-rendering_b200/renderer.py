@@ -7,6 +7,7 @@ ctypes call into libvr5.so; no arithmetic of the hot path lives in Python.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -257,6 +258,30 @@ class GPURenderer5:
     def peer_close(self):
         self._L.vr5_peer_close(self._h)
 
+    # -- host frame ring: every rank copies its strips to shared HOST memory over its own PCIe link (include/vr5.h) --
+    def hostring_attach(self, buffer, slots: int, init: bool):
+        """`buffer`: a writable buffer object (multiprocessing.shared_memory .buf, numpy array, ...) of at least
+        hostring_bytes(width, height, slots) bytes; it must outlive the attachment (hostring_detach / close)."""
+        view = (C.c_char * len(buffer)).from_buffer(buffer)
+        self._hostring_view = view   # keeps the export alive
+        self._check(self._L.vr5_hostring_attach(self._h, C.addressof(view), len(buffer), slots, 1 if init else 0))
+
+    def hostring_render(self, params: Params, seq: int):
+        self._check(self._L.vr5_hostring_render(self._h, C.byref(params), seq))
+
+    def hostring_wait(self, seq: int) -> int:
+        """Blocks until every rank's strips of frame `seq` are in host memory; returns the frame's address in the ring."""
+        p = C.c_void_p()
+        self._check(self._L.vr5_hostring_wait(self._h, seq, C.byref(p)))
+        return p.value
+
+    def hostring_release(self, seq: int):
+        self._check(self._L.vr5_hostring_release(self._h, seq))
+
+    def hostring_detach(self):
+        self._L.vr5_hostring_detach(self._h)
+        self._hostring_view = None
+
     def device_alloc(self, nbytes) -> int:
         p = self._L.vr5_device_alloc(self._h, nbytes)
         if not p:
@@ -285,6 +310,32 @@ class GPURenderer5:
 
 
 # ---- volume files (include/vr5.h "volume files"; host side) ---------------------------------------------------------------
+def hostring_bytes(width: int, height: int, slots: int) -> int:
+    """Size of a host frame ring (header + slots frames), 0 for an invalid slot count (vr5_hostring_bytes)."""
+    return int(lib().vr5_hostring_bytes(width, height, slots))
+
+
+def ring_memory(name: str, nbytes: int, create: bool):
+    """Host memory for a frame ring shared by the ranks of one node: a file in /dev/shm mapped read-write (POSIX shared
+    memory without Python's resource tracker). The creator sizes it; remove it with ring_memory_unlink when all ranks are done."""
+    import mmap
+    path = os.path.join("/dev/shm", name)
+    fd = os.open(path, os.O_RDWR | (os.O_CREAT | os.O_EXCL if create else 0), 0o600)
+    try:
+        if create:
+            os.ftruncate(fd, nbytes)
+        return mmap.mmap(fd, nbytes, mmap.MAP_SHARED, mmap.PROT_READ | mmap.PROT_WRITE)
+    finally:
+        os.close(fd)
+
+
+def ring_memory_unlink(name: str):
+    try:
+        os.unlink(os.path.join("/dev/shm", name))
+    except FileNotFoundError:
+        pass
+
+
 def _take(ptr, nbytes) -> np.ndarray:
     out = np.ctypeslib.as_array(ptr, shape=(nbytes,)).copy() if nbytes else np.zeros(0, dtype=np.uint8)
     lib().vr5_volume_free(C.cast(ptr, C.c_void_p))
