@@ -487,7 +487,7 @@ def run_b200_arm(args, wl):
     k_ms = gpu.render_timed(frames, out_ptr, l2_flush=False)
     k_ms_flushed = gpu.render_timed(frames[: min(len(frames), 24)], out_ptr, l2_flush=True)
     strip_px = (L.vr5_strip_rows(h, rank, world) if world > 1 else h) * w
-    voxel_bytes = 8.0 if args.sampler == "trilinear" else 1.0   # nearest 1 B per fetch, trilinear 8 B
+    voxel_bytes = 8.0 if args.sampler.startswith("trilinear") else 1.0   # nearest 1 B per fetch, trilinear 8 B
     alg_bytes = voxel_bytes * (samples_local + shaded_local) / len(frames) + 4.0 * strip_px  # + 4 B per pixel written
     peak, peak_src = measured_peak()
     achieved = alg_bytes / (float(k_ms.mean()) * 1e-3) / 1e9
@@ -511,10 +511,11 @@ def run_b200_arm(args, wl):
                        "l2": "no flush in the timed loop: per frame the kernel reads the %.0f MB volume and writes the %.1f MB frame (L2 is 126 MB); "
                              "the flushed per-kernel time is reported in roofline.kernel_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_src, "kernel": ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler == "trilinear" else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant())),
+                         "peak_source": peak_src, "kernel": ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler.startswith("trilinear") else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant())),
                          "bytes_per_sample": voxel_bytes, "kernel_ms": float(k_ms.mean()),
                          "kernel_ms_l2_flushed": float(k_ms_flushed.mean()), "algorithmic_bytes_per_launch": alg_bytes,
-                         "note": ("trilinear policy (GPURenderer4 semantics, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear" else
+                         "note": ("trilinear policy, contracted arithmetic (GPURenderer4 semantics as nvcc -fmad=true builds them, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear-fma" else
+                                  "trilinear policy (GPURenderer4 semantics, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear" else
                                   "parity mode fetches 1 B per sample; the kernel is bound by the fp32 pipe and issue slots, not by HBM (DESIGN.md)")},
             "e2e": {"value": samples_total / e2e_s / 1e9, "unit": UNIT, "fps": args.steps / e2e_s, "h2d_bytes_per_step": C.sizeof(R.Params),
                     "d2h_bytes_per_step": w * h * 4,
@@ -559,7 +560,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2", "trilinear"])
+    ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2", "trilinear", "trilinear-fma"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap", type=int, default=4, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how strips reach rank 0")

@@ -63,7 +63,12 @@ enum { VR5_SAMPLER_LINEAR = 0,  /* x-fastest linear array, LDG.U8 (the reference
        /* NOT a parity policy: GPURenderer4's semantics (GPURenderer4.cu:33-97) - trilinear volume fetch, linearly
         * interpolated transfer function - evaluated in software fp32; 8 bytes per sample from an 8-byte-per-cell layout.
         * Checked bit for bit against the restated CPU checker (trilinear section of the test oracle), SURVEY 8(f) rank 2. */
-       VR5_SAMPLER_TRILINEAR = 16 };
+       VR5_SAMPLER_TRILINEAR = 16,
+       /* The same policy and memory layout with CONTRACTED arithmetic: every a + b*c of the march is one fused multiply-add,
+        * as nvcc's default -fmad=true builds the reference's GPU renderers (GPURenderer4.cu:75-86), and the filtering
+        * formulas are evaluated in their fused form (position fma(p, n/2, n/2 - 0.5), lerp fma(w, b - a, a)). Checked bit for
+        * bit against the "trilinear-fma" section of the CPU checker; agrees with VR5_SAMPLER_TRILINEAR within 1 LSB. */
+       VR5_SAMPLER_TRILINEAR_FMA = 18 };
 
 /* ---- lifecycle ------------------------------------------------------------------------------------------ */
 
@@ -98,7 +103,7 @@ int vr5_get_sampler(const vr5_renderer *r);
 /* Memory path the LAST launch actually took: the VR5_SAMPLER_* id of the kernel variant (a window sampler renders a
  * frame through the clamped texture path when the frame's step could leave the guard margin; ids 7..9 are the
  * power-of-two specialisations of 4..6; VR5_SAMPLER_TRILINEAR + 1 is the trilinear march with unclamped 32-bit record
- * addressing, VR5_SAMPLER_TRILINEAR itself the clamped one), -1 before any launch. */
+ * addressing, VR5_SAMPLER_TRILINEAR itself the clamped one, likewise VR5_SAMPLER_TRILINEAR_FMA (+ 1)), -1 before any launch. */
 int vr5_last_variant(const vr5_renderer *r);
 
 /* ---- the hot path ----------------------------------------------------------------------------------------- */

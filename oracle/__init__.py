@@ -103,6 +103,8 @@ class Port:
         L.orc_render_rows.restype = C.c_int
         L.orc_render_rows_trilinear.argtypes = L.orc_render_rows.argtypes
         L.orc_render_rows_trilinear.restype = C.c_int
+        L.orc_render_rows_trilinear_fma.argtypes = L.orc_render_rows.argtypes
+        L.orc_render_rows_trilinear_fma.restype = C.c_int
         L.orc_default_base_tf.argtypes = [C.POINTER(C.c_float)]
         L.orc_premultiply_tf.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.orc_build_esl_bits.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_uint8), C.POINTER(C.c_uint32)]
@@ -116,10 +118,13 @@ class Port:
         L.orc_synth_cos_table.argtypes = [C.POINTER(C.c_int16)]
 
     # -- rendering ---------------------------------------------------------------------------------------
-    def render(self, scene: Scene, rows=None, threads: int | None = None, trilinear: bool = False):
+    def render(self, scene: Scene, rows=None, threads: int | None = None, trilinear=False):
         """Frame (or row range) as uint8 [H, W, 4] plus summed counters; rows are split over host threads.
-        trilinear=True: the restated GPURenderer4 sampler policy (fp32 trilinear volume fetch, linear TF)."""
-        fn = self.lib.orc_render_rows_trilinear if trilinear else self.lib.orc_render_rows
+        trilinear=True: the restated GPURenderer4 sampler policy (fp32 trilinear volume fetch, linear TF), one rounding
+        per operation; trilinear="fma": the same policy with the contractions nvcc applies to the reference's GPU
+        renderers written out as fused multiply-adds."""
+        fn = (self.lib.orc_render_rows_trilinear_fma if trilinear == "fma" else
+              self.lib.orc_render_rows_trilinear if trilinear else self.lib.orc_render_rows)
         w, h = scene.width, scene.height
         row0, row1 = (0, h) if rows is None else rows
         out = np.zeros((h, w, 4), dtype=np.uint8)

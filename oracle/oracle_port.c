@@ -455,3 +455,148 @@ int orc_render_rows_trilinear(const vr5_raycaster *r, uint8_t *rgba8, int row0, 
     if (cnt) *cnt = local;
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Trilinear sampler policy, CONTRACTED arithmetic ("trilinear-fma"). Parity status of THIS section: UNPINNED,
+ * for the same reasons as the section above (GPURenderer4 does not build with CUDA 12; the texture unit filters
+ * in fixed point).
+ *
+ * The reference's GPU renderers are built by nvcc with its default -fmad=true, which contracts every
+ * `a + b*c` of their march loops (GPURenderer4.cu:75-86: `pt = origin + direction*k`, `acc = acc + cur*(1 -
+ * acc.w)`) into one fused multiply-add; only the CPU renderer rounds the product separately. This section
+ * restates the same policy with those contractions written out as fmaf() - one rounding per fused operation -
+ * and with the filtering formulas in their fused form:
+ *
+ *   point:    p = fma(d, k, o) per axis (march loop AND leading empty-space loop); k += step sequentially.
+ *   volume:   texel position t = fma(p, n/2, n/2 - 0.5)  (= (p+1)*0.5*n - 0.5 with ONE rounding; n/2 and
+ *             n/2 - 0.5 are exact), cell floor(t), weight w = t - floor(t), neighbours clamped to [0, n-1],
+ *             lerp x then y then z as fma(w, b - a, a) on the raw byte values -> v in [0, 255].
+ *   TF:       position u = fma(v, RN(128/255), -0.5), entry floor(u), weight u - floor(u), entries clamped to
+ *             [0, 127], per channel fma(w, b - a, a).
+ *   shading:  guard and light vector as GPURenderer4.cu:41-51 in separate roundings (rare path), second fetch
+ *             v_l at p + L*0.01, diffuse = ((v_l - v) * RN(1/255)) * kd.
+ *   blend:    t = 1 - acc.w; acc = fma(cur, t, acc) per channel.
+ *
+ * fmaf() is correctly rounded on every platform (glibc uses the FMA unit where there is one and an exact
+ * software path elsewhere), so this section does not depend on the build's -mfma setting.
+ * ------------------------------------------------------------------------------------------------------- */
+#define ORC_TF_SCALE_255 0x1.010102p-1f /* RN(128 / 255) */
+#define ORC_INV_255 0x1.010102p-8f      /* RN(1 / 255)   */
+
+static inline float lerp_fma(float a, float b, float w) {
+    float d = b - a;
+    return fmaf(w, d, a);
+}
+
+static inline void tri_axis_fma(float p, uint32_t n, int64_t *i0, int64_t *i1, float *w) {
+    float half_n = (float)n * 0.5f;
+    float bias = half_n - 0.5f;
+    float t = fmaf(p, half_n, bias);
+    float fl = floorf(t);
+    *w = t - fl;
+    int64_t a = (int64_t)fl, b = a + 1;
+    if (a < 0) a = 0;
+    if (a > (int64_t)n - 1) a = (int64_t)n - 1;
+    if (b < 0) b = 0;
+    if (b > (int64_t)n - 1) b = (int64_t)n - 1;
+    *i0 = a; *i1 = b;
+}
+
+/* trilinear value on the byte scale, [0, 255] */
+static inline float fetch_trilinear_fma(const vr5_model *m, float px, float py, float pz) {
+    int64_t x0, x1, y0, y1, z0, z1;
+    float wx, wy, wz;
+    tri_axis_fma(px, m->dims.x, &x0, &x1, &wx);
+    tri_axis_fma(py, m->dims.y, &y0, &y1, &wy);
+    tri_axis_fma(pz, m->dims.z, &z0, &z1, &wz);
+    const uint64_t sx = m->dims.x, sxy = (uint64_t)m->dims.x * m->dims.y;
+#define VOX(X, Y, Z) ((float)m->data[(uint64_t)(Z) * sxy + (uint64_t)(Y) * sx + (uint64_t)(X)])
+    float c00 = lerp_fma(VOX(x0, y0, z0), VOX(x1, y0, z0), wx);
+    float c10 = lerp_fma(VOX(x0, y1, z0), VOX(x1, y1, z0), wx);
+    float c01 = lerp_fma(VOX(x0, y0, z1), VOX(x1, y0, z1), wx);
+    float c11 = lerp_fma(VOX(x0, y1, z1), VOX(x1, y1, z1), wx);
+#undef VOX
+    float c0 = lerp_fma(c00, c10, wy);
+    float c1 = lerp_fma(c01, c11, wy);
+    return lerp_fma(c0, c1, wz);
+}
+
+static inline vr5_f4 classify_linear_fma(const vr5_f4 *tf, float v) {
+    float u = fmaf(v, ORC_TF_SCALE_255, -0.5f);
+    float fl = floorf(u);
+    float w = u - fl;
+    int j0 = (int)fl, j1 = j0 + 1;
+    if (j0 < 0) j0 = 0;
+    if (j0 > VR5_TF_SIZE - 1) j0 = VR5_TF_SIZE - 1;
+    if (j1 < 0) j1 = 0;
+    if (j1 > VR5_TF_SIZE - 1) j1 = VR5_TF_SIZE - 1;
+    vr5_f4 a = tf[j0], b = tf[j1], c;
+    c.x = lerp_fma(a.x, b.x, w); c.y = lerp_fma(a.y, b.y, w); c.z = lerp_fma(a.z, b.z, w); c.w = lerp_fma(a.w, b.w, w);
+    return c;
+}
+
+static void cast_pixel_trilinear_fma(const vr5_raycaster *r, uint8_t *rgba8, int col, int row, orc_counters *cnt) {
+    vr5_f3 o, d;
+    float k, k_far;
+    primary_ray(&r->view, col, row, &o, &d);
+    if (!clip_ray(&r->volume, o, d, &k, &k_far)) return;
+    cnt->rays_hit++;
+    float px = fmaf(d.x, k, o.x), py = fmaf(d.y, k, o.y), pz = fmaf(d.z, k, o.z);
+    while (k <= k_far) {
+        if (r->esl && block_is_empty(r, px, py, pz)) {
+            k += leap_distance(r, px, py, pz, d);
+            cnt->esl_iters++;
+        } else {
+            break;
+        }
+        k += r->ray_step;
+        px = fmaf(d.x, k, o.x); py = fmaf(d.y, k, o.y); pz = fmaf(d.z, k, o.z);
+    }
+    if (k > k_far) return;
+    cnt->rays_accum++;
+    vr5_f4 acc = {0, 0, 0, 0};
+    while (k <= k_far) {
+        float v = fetch_trilinear_fma(&r->volume, px, py, pz);
+        vr5_f4 cur = classify_linear_fma(r->transfer_fn, v);
+        cnt->samples++;
+        if (cur.w > 0.05f && r->light_kd > 0.01f) {
+            float lx = r->view.light_pos.x - px, ly = r->view.light_pos.y - py, lz = r->view.light_pos.z - pz;
+            float xx = lx * lx, yy = ly * ly, zz = lz * lz;
+            float s = xx + yy;
+            s = s + zz;
+            float inv = 1.0f / sqrtf(s);
+            float nx = lx * inv, ny = ly * inv, nz = lz * inv;
+            float ox = nx * 0.01f, oy = ny * 0.01f, oz = nz * 0.01f;
+            float qx = px + ox, qy = py + oy, qz = pz + oz;
+            float v_l = fetch_trilinear_fma(&r->volume, qx, qy, qz);
+            float diff = v_l - v;
+            diff = diff * ORC_INV_255;
+            diff = diff * r->light_kd;
+            cur.x += diff; cur.y += diff; cur.z += diff;
+            cnt->shaded++;
+        }
+        float t = 1 - acc.w;
+        acc.x = fmaf(cur.x, t, acc.x); acc.y = fmaf(cur.y, t, acc.y); acc.z = fmaf(cur.z, t, acc.z); acc.w = fmaf(cur.w, t, acc.w);
+        if (acc.w > r->ray_threshold) break;
+        k += r->ray_step;
+        px = fmaf(d.x, k, o.x); py = fmaf(d.y, k, o.y); pz = fmaf(d.z, k, o.z);
+    }
+    uint8_t *px8 = rgba8 + 4 * ((size_t)row * r->view.dims.x + (size_t)col);
+    px8[0] = (uint8_t)unit_to_index(acc.x, 256);
+    px8[1] = (uint8_t)unit_to_index(acc.y, 256);
+    px8[2] = (uint8_t)unit_to_index(acc.z, 256);
+    px8[3] = (uint8_t)unit_to_index(acc.w, 256);
+}
+
+int orc_render_rows_trilinear_fma(const vr5_raycaster *r, uint8_t *rgba8, int row0, int row1, orc_counters *cnt) {
+    if (r->volume.data == NULL || r->transfer_fn == NULL || r->esl_volume == NULL || rgba8 == NULL) return 1;
+    orc_counters local = {0, 0, 0, 0, 0};
+    int w = r->view.dims.x, h = r->view.dims.y;
+    if (row0 < 0) row0 = 0;
+    if (row1 > h) row1 = h;
+    if (row1 > row0) memset(rgba8 + (size_t)row0 * w * 4, 0, (size_t)(row1 - row0) * w * 4);
+    for (int row = row0; row < row1; row++)
+        for (int col = 0; col < w; col++) cast_pixel_trilinear_fma(r, rgba8, col, row, &local);
+    if (cnt) *cnt = local;
+    return 0;
+}

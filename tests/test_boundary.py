@@ -99,11 +99,22 @@ def test_product_never_imports_the_oracle():
 
 
 def test_kernel_has_no_fused_multiply_add_in_ray_math():
-    """-fmad=false is part of the parity contract; the only FFMA in the cast kernels may come from the IEEE division /
-    square-root sequences (FCHK/MUFU neighbourhood), never from packed FFMA2 contraction."""
+    """-fmad=false is part of the parity contract; the only FFMA in the parity kernels may come from the IEEE division /
+    square-root sequences (FCHK/MUFU neighbourhood), never from packed FFMA2 contraction. The one place a packed FMA is
+    legitimate is the contracted trilinear policy (tri_kernel<..., FMA=true>), whose fusions are explicit."""
     lib = os.path.join(ROOT, "volume-rendering_b200", "libvr5.so")
     sass = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
     assert "cast_kernel" in sass
-    assert "FFMA2" not in sass
+    with_ffma2 = set()
+    fn = None
+    for line in sass.splitlines():
+        if "Function :" in line:
+            fn = line.split("Function :")[1].strip()
+        elif "FFMA2" in line and fn:
+            with_ffma2.add(fn)
+    # mangled template arguments of tri_kernel: COUNT, FAST, SHADE, FMA, MINB -> ...ILb?ELb?ELb?ELb1ELi?EE...
+    bad = [f for f in with_ffma2 if not re.search(r"tri_kernelILb[01]ELb[01]ELb[01]ELb1ELi\d+EE", f)]
+    assert not bad, bad
+    assert any("tri_kernel" in f for f in with_ffma2)  # the contracted march does use the packed FMA
     mk = open(os.path.join(CSRC, "Makefile")).read()
     assert "-fmad=false" in mk and "use_fast_math" not in mk.replace("Never --use_fast_math", "")

@@ -2,7 +2,9 @@
 
 The CPU side is oracle_port.c's trilinear section ("parity unpinned": GPURenderer4 cannot be built with CUDA 12 and its
 filtering runs in the texture unit's fixed point). The CUDA policy VR5_SAMPLER_TRILINEAR performs the same fp32 operations
-in the same order and is held to bit equality with that restatement."""
+in the same order and is held to bit equality with that restatement. VR5_SAMPLER_TRILINEAR_FMA is the same policy with the
+contractions nvcc applies to the reference's GPU renderers written out as fused multiply-adds; it is held to bit equality
+with the checker's "trilinear-fma" section and to the stated LSB tolerance against the one-rounding-per-operation policy."""
 import os
 import subprocess
 
@@ -36,6 +38,58 @@ def test_oracle_trilinear_is_smooth_where_nearest_steps(port, bucky, golden):
     assert 0 < d.max() and d.mean() < 12
 
 
+def test_oracle_trilinear_fma_agrees_with_separate_roundings(port, bucky, golden):
+    """The contracted restatement differs from the one-rounding-per-operation restatement only by rounding: same rays, same
+    sample counts, frames within the stated tolerance (<= 1 LSB on >= 99.9 % of pixels, <= 2 LSB max), and not identical."""
+    differing = 0
+    for name in ["bucky_ortho_0_0_0", "bucky_persp_-45_-45_0"]:
+        case = next(c for c in golden["cases"] if c["name"] == name)
+        sc = golden_scene(port, case, bucky)
+        tri, ct = port.render(sc, trilinear=True)
+        fma, cf = port.render(sc, trilinear="fma")
+        assert ct == cf and cf["samples"] > 0
+        differing += assert_parity(fma, tri, exact=False, what=name)["differing"]
+    assert differing > 0
+
+
+def test_oracle_trilinear_fma_constant_volume(port, R):
+    """Constant volume, constant transfer function: every fused lerp returns its operand exactly (w * 0 + a), so the frame
+    is the closed-form blend acc <- fma(c, 1 - acc.a, acc) repeated `samples` times per ray."""
+    vol = np.full((24, 24, 24), 137, dtype=np.uint8)
+    rgba = np.array([0.3, 0.6, 0.9, 0.02], dtype=np.float32)
+    base = np.tile(rgba, (128, 1))
+    ref_view = oracle.View.from_buffer_copy(bytes(R.camera(96, 64, 0, (10.0, 25.0, 0.0), 2.0)))
+    sc = port.make_scene(vol, base, ref_view, light_kd=0.0, esl=False)
+    frame, cnt = port.render(sc, trilinear="fma")
+    near, cn = port.render(sc)
+    assert cnt["rays_accum"] == cn["rays_accum"] > 0
+    from fractions import Fraction
+
+    def round32(x: Fraction) -> np.float32:  # correctly rounded (nearest, ties to even) fp32 of an exact positive rational
+        if x == 0:
+            return np.float32(0.0)
+        e = x.numerator.bit_length() - x.denominator.bit_length()
+        if Fraction(2) ** e > x:
+            e -= 1
+        scaled = x / Fraction(2) ** (e - 23)
+        n = scaled.numerator // scaled.denominator
+        rem = scaled - n
+        if rem > Fraction(1, 2) or (rem == Fraction(1, 2) and n % 2 == 1):
+            n += 1
+        return np.float32(float(Fraction(n) * Fraction(2) ** (e - 23)))
+
+    tf0 = np.asarray(sc.tf, dtype=np.float32).reshape(128, 4)[64]
+    acc = [np.float32(0.0)] * 4
+    seen = set()
+    for _ in range(200):  # more samples than any ray through a 24^3 grid takes
+        t = np.float32(1.0) - acc[3]
+        acc = [round32(Fraction(float(c)) * Fraction(float(t)) + Fraction(float(a))) for c, a in zip(tf0, acc)]
+        seen.add(tuple(min(int(np.float32(a) * np.float32(256.0)), 255) for a in acc))
+    lit = frame.reshape(-1, 4)
+    lit = lit[lit[:, 3] > 0]
+    assert len(lit) > 0 and all(tuple(int(v) for v in px) in seen for px in np.unique(lit, axis=0))
+
+
 def test_division_by_255_identity(tmp_path):
     """vr5_tri.cuh computes sample / 255 as two FMAs around a multiplication by RN(1/255). The identity with the IEEE
     division holds for every float in [0, 255] (tools/check_div255.c without an argument checks all 1.13e9 of them); here a
@@ -47,10 +101,14 @@ def test_division_by_255_identity(tmp_path):
     assert "0 mismatches" in out, out
 
 
+POLICIES = [("trilinear", True, 16), ("trilinear-fma", "fma", 18)]  # sampler name, checker mode, base variant id
+
+
 @pytest.mark.gpu
+@pytest.mark.parametrize("policy", POLICIES, ids=[p[0] for p in POLICIES])
 @pytest.mark.parametrize("clamped", [False, True])
 @pytest.mark.parametrize("name", ["bucky_ortho_0_0_0", "bucky_persp_-45_-45_0", "synthA64_default_persp"])
-def test_gpu_trilinear_matches_restated_oracle(name, clamped, golden, port, volumes, R, monkeypatch):
+def test_gpu_trilinear_matches_restated_oracle(name, clamped, policy, golden, port, volumes, R, monkeypatch):
     """Both marches - unclamped 32-bit record addressing (cubic volumes whose step stays inside the guard cells; variant 17)
     and the clamped one (variant 16, forced here through its knob) - against the restatement, bit for bit."""
     if clamped:
@@ -58,27 +116,49 @@ def test_gpu_trilinear_matches_restated_oracle(name, clamped, golden, port, volu
     case = next(c for c in golden["cases"] if c["name"] == name)
     sc = golden_scene(port, case, volumes(case["volume"]))
     scene, params = product_scene(R, sc)
-    gpu = R.GPURenderer5(0, sampler="trilinear")
+    sampler, mode, base_variant = policy
+    gpu = R.GPURenderer5(0, sampler=sampler)
     try:
         gpu.set_window_buffer(case["width"], case["height"])
         gpu.set_scene(scene)
         frame = gpu.render_volume(params)
-        want, cnt = port.render(sc, trilinear=True)
+        want, cnt = port.render(sc, trilinear=mode)
         assert_parity(frame, want, exact=True, what=name)
-        assert gpu.last_variant() == (16 if clamped else 17)
+        assert gpu.last_variant() == base_variant + (0 if clamped else 1)
         assert gpu.count(params) == cnt
     finally:
         gpu.close()
 
 
 @pytest.mark.gpu
-def test_gpu_trilinear_ragged_random(port, R):
+@pytest.mark.parametrize("ctas", ["5", "4"])
+def test_gpu_trilinear_fma_register_budget_variants(ctas, golden, port, volumes, R, monkeypatch):
+    """The contracted unclamped march is built for three register budgets (VR5_TRIF_CTAS = 6 default, 5, 4): same bits."""
+    monkeypatch.setenv("VR5_TRIF_CTAS", ctas)
+    case = next(c for c in golden["cases"] if c["name"] == "synthA64_semi_ortho")
+    sc = golden_scene(port, case, volumes(case["volume"]))
+    scene, params = product_scene(R, sc)
+    gpu = R.GPURenderer5(0, sampler="trilinear-fma")
+    try:
+        gpu.set_window_buffer(case["width"], case["height"])
+        gpu.set_scene(scene)
+        frame = gpu.render_volume(params)
+        want, _ = port.render(sc, trilinear="fma")
+        assert_parity(frame, want, exact=True, what=ctas)
+        assert gpu.last_variant() == 19
+    finally:
+        gpu.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("policy", POLICIES, ids=[p[0] for p in POLICIES])
+def test_gpu_trilinear_ragged_random(policy, port, R):
     """Non-cubic random volume (worst case for interpolation: neighbours uncorrelated), ragged viewports, every TF preset,
     both projections, shading on and off, partition strips."""
     rng = np.random.default_rng(5)
     vol = rng.integers(0, 256, size=(29, 41, 66), dtype=np.uint8)
     vol[:, :13] = 0
-    gpu = R.GPURenderer5(0, sampler="trilinear")
+    gpu = R.GPURenderer5(0, sampler=policy[0])
     try:
         for tf_name, kw in [("default", {}), ("opaque", {}), ("semi", {"ray_threshold": 1.0, "light_kd": 0.0}), ("default", {"esl": False})]:
             base = {"default": R.default_base_tf(), "opaque": R.tf_opaque(), "semi": R.tf_semi(66)}[tf_name]
@@ -93,7 +173,7 @@ def test_gpu_trilinear_ragged_random(port, R):
                 frame = gpu.render_volume(params)
                 osc = port.make_scene(vol, tf_by_name(port, tf_name, 66), oracle.View.from_buffer_copy(bytes(view)),
                                       threshold=scene.ray_threshold, esl=scene.esl, light_kd=scene.light_kd)
-                want, cnt = port.render(osc, trilinear=True)
+                want, cnt = port.render(osc, trilinear=policy[1])
                 assert_parity(frame, want, exact=True, what=(tf_name, persp, ang))
                 assert gpu.count(params) == cnt
     finally:

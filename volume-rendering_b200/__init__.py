@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(HERE, "libvr5.so")
 CSRC = os.path.join(HERE, "csrc")
 
 SAMPLER_LINEAR, SAMPLER_BRICK, SAMPLER_TEX3D, SAMPLER_HYBRID = 0, 1, 2, 3
-SAMPLERS = {"linear": 0, "brick": 1, "tex3d": 2, "hybrid": 3, "hybridw": 4, "window": 5, "hybridw2": 6, "trilinear": 16}
+SAMPLERS = {"linear": 0, "brick": 1, "tex3d": 2, "hybrid": 3, "hybridw": 4, "window": 5, "hybridw2": 6, "trilinear": 16, "trilinear-fma": 18}
 
 
 class Vr5Error(RuntimeError):

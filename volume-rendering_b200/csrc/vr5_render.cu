@@ -232,6 +232,7 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
         else if (!strcmp(env, "window") || !strcmp(env, "5")) r->sampler = VR5_SAMPLER_WINDOW;
         else if (!strcmp(env, "hybridw2") || !strcmp(env, "6")) r->sampler = VR5_SAMPLER_HYBRID_WINDOW2;
         else if (!strcmp(env, "trilinear") || !strcmp(env, "16")) r->sampler = VR5_SAMPLER_TRILINEAR;
+        else if (!strcmp(env, "trilinear-fma") || !strcmp(env, "18")) r->sampler = VR5_SAMPLER_TRILINEAR_FMA;
     }
     *out = r;
     return 0;
@@ -489,10 +490,12 @@ static int build_p2(vr5_renderer *r) {
     return 0;
 }
 
+static inline bool is_trilinear(int sampler) { return sampler == VR5_SAMPLER_TRILINEAR || sampler == VR5_SAMPLER_TRILINEAR_FMA; }
+
 static int build_layout(vr5_renderer *r) {
     free_layouts(r);
     if (!r->d_vol_linear) return 0;
-    if (r->sampler == VR5_SAMPLER_TRILINEAR) {
+    if (is_trilinear(r->sampler)) {
         const uint64_t bytes = (uint64_t)(r->nx + 1 + 2 * kTriGuard) * (r->ny + 1 + 2 * kTriGuard) * (r->nz + 1 + 2 * kTriGuard) * 8u;
         // the unclamped march wants the array inside one 4-GiB address window: an allocation that straddles one is retried
         uint8_t *held[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -622,7 +625,7 @@ extern "C" int vr5_get_volume(vr5_renderer *r, uint8_t *host_out, uint64_t bytes
 
 extern "C" int vr5_set_sampler(vr5_renderer *r, int sampler) {
     if (!r) return 1;
-    if (sampler < 0 || (sampler > VR5_SAMPLER_HYBRID_WINDOW2 && sampler != VR5_SAMPLER_TRILINEAR)) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (sampler < 0 || (sampler > VR5_SAMPLER_HYBRID_WINDOW2 && !is_trilinear(sampler))) { vr5_fail(r, "vr5_set_sampler: unknown sampler", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     VR5_CUDA(r, sync_all(r));
     if (sampler == r->sampler && (r->d_vol_padded || r->d_vol_brick || r->tex || r->d_vol_window || r->p2_wl || r->d_cells || !r->d_vol_linear)) return 0;
@@ -789,7 +792,7 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
     // the padded layouts may be indexed without the upper clamp when rays are clipped to the cube they cover
     const bool cube = a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f;
     cudaError_t e;
-    if (r->sampler == VR5_SAMPLER_TRILINEAR) {  // GPURenderer4 semantics in software fp32 (vr5_tri.cuh)
+    if (is_trilinear(r->sampler)) {  // GPURenderer4 semantics in software fp32 (vr5_tri.cuh); _FMA: contracted arithmetic
         TriArgs t;
         t.cells = reinterpret_cast<const uint2 *>(r->d_cells);
         t.cx = r->nx + 1 + 2 * kTriGuard; t.cy = r->ny + 1 + 2 * kTriGuard;
@@ -805,10 +808,20 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
         // one march step may leave the cube by step * |d| * n/2 cells per axis (+1 for the cell's far corner, +1 rounding)
         const bool fast = one_window && cube && !count && !getenv("VR5_TRI_CLAMPED") && reach_ok(a, (float)(kTriGuard - 2));
         // variants: instrumented (clamped, shading code present), and {clamped, unclamped} x {shading code, none}
-        const int v = count ? 0 : 1 + (fast ? 2 : 0) + (shade ? 1 : 0);
-        void (*const kernels[5])(const KArgs, const TriArgs) = {tri_kernel<true, false, true>, tri_kernel<false, false, false>, tri_kernel<false, false, true>,
-                                                                tri_kernel<false, true, false>, tri_kernel<false, true, true>};
-        int &per_sm = r->ctas_per_sm[507 + v];
+        const bool fused = r->sampler == VR5_SAMPLER_TRILINEAR_FMA;
+        int v = (count ? 0 : 1 + (fast ? 2 : 0) + (shade ? 1 : 0)) + (fused ? 5 : 0);
+        if (v == 8) {  // contracted, unclamped, no shading code: register budget knob (default from profiles/r01_sampler_choice.md)
+            const char *env = getenv("VR5_TRIF_CTAS");
+            const int want = env ? atoi(env) : 6;
+            v = want == 5 ? 10 : want == 4 ? 11 : 8;
+        }
+        void (*const kernels[12])(const KArgs, const TriArgs) = {
+            tri_kernel<true, false, true, false>, tri_kernel<false, false, false, false>, tri_kernel<false, false, true, false>,
+            tri_kernel<false, true, false, false>, tri_kernel<false, true, true, false>,
+            tri_kernel<true, false, true, true>, tri_kernel<false, false, false, true>, tri_kernel<false, false, true, true>,
+            tri_kernel<false, true, false, true>, tri_kernel<false, true, true, true>,
+            tri_kernel<false, true, false, true, 5>, tri_kernel<false, true, false, true, 4>};
+        int &per_sm = r->ctas_per_sm[500 + v];
         if (per_sm == 0) {
             e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernels[v], kCtaThreads, 0);
             if (e != cudaSuccess || per_sm < 1) per_sm = 1;
@@ -820,7 +833,7 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
         r->tri_fast = fast ? 1 : 0;
         r->last_grid = grid;
         r->launches++;
-        r->last_variant = VR5_SAMPLER_TRILINEAR + (fast ? 1 : 0);
+        r->last_variant = r->sampler + (fast ? 1 : 0);
         e = cudaGetLastError();
         if (e != cudaSuccess) { vr5_fail(r, "tri_kernel launch", e, __FILE__, __LINE__); return 1; }
         return 0;

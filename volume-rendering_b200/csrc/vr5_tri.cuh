@@ -30,7 +30,7 @@ struct TriArgs {
 #ifndef VR5_TRI_PIN
 #define VR5_TRI_PIN 1
 #endif
-struct TriRegs { float step, threshold, hfx, hfy, hfz; uint32_t s1, s2, c0, hi, pair_c; };
+struct TriRegs { float step, threshold, hfx, hfy, hfz; uint32_t s1, s2, c0, hi, pair_c; float bfx, bfy, bfz; };  // bf = hf - 0.5 (contracted policy)
 
 // one axis: texel position t = ((p + 1) * 0.5) * n - 0.5, cell floor(t), weight t - floor(t). floor() comes from an add
 // rounded toward -inf against 1.5 * 2^23, whose bit pattern also carries the integer. Returns the biased bits.
@@ -110,7 +110,92 @@ __device__ __forceinline__ float4 tri_classify(uint32_t pair_c, float s) {
     return make_float4(fadd(a.x, fmul(w, d.x)), fadd(a.y, fmul(w, d.y)), fadd(a.z, fmul(w, d.z)), fadd(a.w, fmul(w, d.w)));
 }
 
-template <bool COUNT, bool FAST, bool SHADE>
+// ---- contracted arithmetic (VR5_SAMPLER_TRILINEAR_FMA) ----------------------------------------------------------------
+// The same policy with every a + b*c of the march written as ONE fused multiply-add, as nvcc's default -fmad=true builds the
+// reference's GPU renderers (GPURenderer4.cu:75-86), and the filtering formulas in their fused form (the CPU checker's
+// "trilinear-fma" section spells the operations out). The TU is still compiled with -fmad=false: every fusion below is an
+// explicit fma, and x/y of a point, the four x-lerps and the colour pairs go through the packed f32x2 forms (FFMA2 / FADD2).
+constexpr float kTfScale255 = 0x1.010102p-1f;  // RN(128 / 255)
+constexpr float kInv255 = 0x1.010102p-8f;      // RN(1 / 255)
+
+// packed pairs as float2 through the sm_100 intrinsics (FFMA2 / FADD2, every rounding mode); negation is an operand modifier
+__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __fadd2_rn(a, neg2(b)); }
+__device__ __forceinline__ float2 both(float v) { return make_float2(v, v); }
+
+template <bool FMA>
+__device__ __forceinline__ float ray_point(float o, float d, float k) { return FMA ? __fmaf_rn(d, k, o) : fadd(o, fmul(d, k)); }
+
+// one axis, fused: t = fma(p, n/2, n/2 - 0.5), cell floor(t), weight t - floor(t); returns the biased bits of RD(t + magic)
+__device__ __forceinline__ uint32_t trif_axis(float p, float hf, float bf, float &w) {
+    const float t = __fmaf_rn(p, hf, bf);
+    const float tm = __fadd_rd(t, kTriMagic);
+    w = fsub(t, fsub(tm, kTriMagic));
+    return __float_as_uint(tm);
+}
+
+__device__ __forceinline__ void trif_load(const TriArgs &t, const TriRegs &g, uint32_t bx, uint32_t by, uint32_t bz, bool fast, uint2 &c) {
+    if (fast) {
+        uint32_t lo;
+        asm("{\n\t.reg .u32 t;\n\tmad.lo.u32 t, %3, %5, %6;\n\tmad.lo.u32 t, %2, %4, t;\n\tshl.b32 %0, %1, 3;\n\tadd.u32 %0, %0, t;\n\t}"
+            : "=r"(lo) : "r"(bx), "r"(by), "r"(bz), "r"(g.s1), "r"(g.s2), "r"(g.c0));
+        // volatile: the request stays where it is written, ahead of the current sample's arithmetic (ptxas otherwise sinks it below
+        // the early-termination branch, to the end of the iteration, and the next iteration starts on its latency)
+        asm volatile("{\n\t.reg .u64 p;\n\tmov.b64 p, {%2, %3};\n\tld.global.nc.v2.u32 {%0, %1}, [p];\n\t}" : "=r"(c.x), "=r"(c.y) : "r"(lo), "r"(g.hi));
+    } else {
+        const int bias = (int)kTriMagicBits - 1 - kTriGuard;
+        const uint32_t jx = (uint32_t)min(max((int)bx - bias, 0), (int)t.jx1);
+        const uint32_t jy = (uint32_t)min(max((int)by - bias, 0), (int)t.jy1);
+        const uint32_t jz = (uint32_t)min(max((int)bz - bias, 0), (int)t.jz1);
+        c = __ldg(t.cells + (((uint64_t)jz * t.cy + jy) * t.cx + jx));
+    }
+}
+
+// request with x and y packed (march loop) and all-scalar (first sample, shading sample)
+struct TriTap2 { uint2 c; float2 wxy; float wz; };
+template <bool FAST>
+__device__ __forceinline__ TriTap2 trif_request2(const TriArgs &t, const TriRegs &g, float2 pxy, float pz, float2 hfxy, float2 bfxy) {
+    TriTap2 tap;
+    const float2 t2 = __ffma2_rn(pxy, hfxy, bfxy);
+    const float2 tm2 = __fadd2_rd(t2, both(kTriMagic));
+    tap.wxy = sub2(t2, __fadd2_rn(tm2, both(-kTriMagic)));
+    const uint32_t bz = trif_axis(pz, g.hfz, g.bfz, tap.wz);
+    trif_load(t, g, __float_as_uint(tm2.x), __float_as_uint(tm2.y), bz, FAST, tap.c);
+    return tap;
+}
+__device__ __forceinline__ TriTap2 trif_request(const TriArgs &t, const TriRegs &g, float px, float py, float pz) {
+    TriTap2 tap;
+    const uint32_t bx = trif_axis(px, g.hfx, g.bfx, tap.wxy.x), by = trif_axis(py, g.hfy, g.bfy, tap.wxy.y), bz = trif_axis(pz, g.hfz, g.bfz, tap.wz);
+    trif_load(t, g, bx, by, bz, false, tap.c);
+    return tap;
+}
+
+// trilinear value on the byte scale: x-lerps of the z0 / z1 face pairs packed, then y packed, then z
+__device__ __forceinline__ float trif_resolve(const TriTap2 &tap) {
+    const uint2 c = tap.c;
+    const float2 a0 = make_float2(byte_biased(c.x, 0), byte_biased(c.y, 0)), b0 = make_float2(byte_biased(c.x, 1), byte_biased(c.y, 1));  // y0 row: (z0, z1)
+    const float2 a1 = make_float2(byte_biased(c.x, 2), byte_biased(c.y, 2)), b1 = make_float2(byte_biased(c.x, 3), byte_biased(c.y, 3));  // y1 row
+    const float2 wx2 = both(tap.wxy.x), wy2 = both(tap.wxy.y);
+    const float2 p = __ffma2_rn(wx2, sub2(b0, a0), __fadd2_rn(a0, both(-8388608.0f)));  // (c00, c01); b - a of the biased values is b - a (exact)
+    const float2 q = __ffma2_rn(wx2, sub2(b1, a1), __fadd2_rn(a1, both(-8388608.0f)));  // (c10, c11)
+    const float2 r = __ffma2_rn(wy2, sub2(q, p), p);
+    return __fmaf_rn(tap.wz, fsub(r.y, r.x), r.x);
+}
+
+// linear TF on the byte-scale value: position fma(v, 128/255, -0.5), same pair table as tri_classify
+__device__ __forceinline__ void trif_classify(uint32_t pair_c, float v, float2 &crg, float2 &cba) {
+    const float u = __fmaf_rn(v, kTfScale255, -0.5f);
+    const float um = __fadd_rd(u, kTriMagic);
+    const float w = fsub(u, fsub(um, kTriMagic));
+    const uint32_t addr = pair_c + (__float_as_uint(um) << 5);
+    float4 a, d;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(addr));
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr));
+    crg = __ffma2_rn(both(w), make_float2(d.x, d.y), make_float2(a.x, a.y));
+    cba = __ffma2_rn(both(w), make_float2(d.z, d.w), make_float2(a.z, a.w));
+}
+
+template <bool COUNT, bool FAST, bool SHADE, bool FMA>
 __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, int col, int row,
                                                  Counters &cnt) {
     // View::get_ray, Raycaster::intersect and the leading empty-space loop are those of the nearest path (vr5_cast.cuh)
@@ -138,7 +223,7 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
         if (!((k < k_far) && (k_far > 0.0f))) return 0u;
     }
     if (COUNT) cnt.rays_hit++;
-    float px = fadd(ox, fmul(dx, k)), py = fadd(oy, fmul(dy, k)), pz = fadd(oz, fmul(dz, k));
+    float px = ray_point<FMA>(ox, dx, k), py = ray_point<FMA>(oy, dy, k), pz = ray_point<FMA>(oz, dz, k);
     const float step = g.step;
     if (a.esl) {
         while (k <= k_far) {
@@ -161,12 +246,53 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
             k = fadd(k, dk);
             if (COUNT) cnt.esl_iters++;
             k = fadd(k, step);
-            px = fadd(ox, fmul(dx, k)); py = fadd(oy, fmul(dy, k)); pz = fadd(oz, fmul(dz, k));
+            px = ray_point<FMA>(ox, dx, k); py = ray_point<FMA>(oy, dy, k); pz = ray_point<FMA>(oz, dz, k);
         }
         if (k > k_far) return 0u;
     }
     if (COUNT) cnt.rays_accum++;
     if (!(k <= k_far)) return 0u;
+    if (FMA) {
+        // contracted march: accumulators and colours live in packed pairs (r,g) / (b,a)
+        float2 acc_rg = make_float2(0.0f, 0.0f), acc_ba = acc_rg;
+        const float2 oxy = make_float2(ox, oy), dxy = make_float2(dx, dy), hfxy = make_float2(g.hfx, g.hfy), bfxy = make_float2(g.bfx, g.bfy);
+        TriTap2 tap = trif_request(t, g, px, py, pz);
+        bool more;
+        do {  // k <= k_far holds on entry (checked above); ONE exit test at the bottom keeps the body a single basic block, so the
+              // scheduler is free to issue the next cell's load ahead of this sample's arithmetic
+            const float kn = fadd(k, step);
+            const float2 nxy = __ffma2_rn(dxy, both(kn), oxy);
+            const float nz = __fmaf_rn(dz, kn, oz);
+            const TriTap2 next = trif_request2<FAST>(t, g, nxy, nz, hfxy, bfxy);
+            const float v = trif_resolve(tap);
+            float2 crg, cba;
+            trif_classify(g.pair_c, v, crg, cba);
+            if (COUNT) cnt.samples++;
+            if (SHADE) {
+                if (cba.y > a.shade_alpha) {
+                    const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
+                    const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
+                    const float inv = fdiv(1.0f, __fsqrt_rn(len2));
+                    const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
+                    const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
+                    const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
+                    const float vl = trif_resolve(trif_request(t, g, qx, qy, qz));
+                    const float diffuse = fmul(fmul(fsub(vl, v), kInv255), a.kd);
+                    crg = make_float2(fadd(crg.x, diffuse), fadd(crg.y, diffuse));
+                    cba.x = fadd(cba.x, diffuse);
+                    if (COUNT) cnt.shaded++;
+                }
+                px = nxy.x; py = nxy.y; pz = nz;
+            }
+            const float2 tr2 = both(fsub(1.0f, acc_ba.y));
+            acc_rg = __ffma2_rn(crg, tr2, acc_rg);
+            acc_ba = __ffma2_rn(cba, tr2, acc_ba);
+            more = !(acc_ba.y > g.threshold) & (kn <= k_far);  // early ray termination (strict >), then while (k <= k_far)
+            k = kn; tap = next;
+        } while (more);
+        return trunc_clamp(fmul(acc_rg.x, 256.0f), 255u) | (trunc_clamp(fmul(acc_rg.y, 256.0f), 255u) << 8) |
+               (trunc_clamp(fmul(acc_ba.x, 256.0f), 255u) << 16) | (trunc_clamp(fmul(acc_ba.y, 256.0f), 255u) << 24);
+    }
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
     // software pipelined like the nearest path: the cell of sample i + 1 is requested before sample i is interpolated and
     // composited (speculative past k_far: the record index is clamped, or - FAST - the host has checked that one step stays
@@ -202,8 +328,9 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
 }
 
 // same persistent-warp / tile-queue skeleton as cast_kernel
-template <bool COUNT, bool FAST, bool SHADE>
-__global__ void __launch_bounds__(kCtaThreads, SHADE ? 0 : 6) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
+// MINB = resident CTAs per SM the register budget is cut for (0: none; 6 = 40 registers, 5 = 48, 4 = 64)
+template <bool COUNT, bool FAST, bool SHADE, bool FMA, int MINB = (SHADE ? 0 : 6)>
+__global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
     __shared__ float4 s_pair[kTriPairs][2];
     __shared__ uint32_t s_esl[1024];
     for (int i = threadIdx.x; i < kTriPairs; i += kCtaThreads) {
@@ -217,12 +344,12 @@ __global__ void __launch_bounds__(kCtaThreads, SHADE ? 0 : 6) tri_kernel(const _
     const uint32_t pair_c = (uint32_t)__cvta_generic_to_shared(&s_pair[0][0]) - ((kTriMagicBits - 1u) << 5);
 #if VR5_TRI_PIN
     __shared__ TriRegs s_regs;
-    if (threadIdx.x == 0) s_regs = TriRegs{a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c};
+    if (threadIdx.x == 0) s_regs = TriRegs{a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c, fsub(t.hfx, 0.5f), fsub(t.hfy, 0.5f), fsub(t.hfz, 0.5f)};
     __syncthreads();
     const volatile TriRegs *vr = &s_regs;
-    const TriRegs g = {vr->step, vr->threshold, vr->hfx, vr->hfy, vr->hfz, vr->s1, vr->s2, vr->c0, vr->hi, vr->pair_c};
+    const TriRegs g = {vr->step, vr->threshold, vr->hfx, vr->hfy, vr->hfz, vr->s1, vr->s2, vr->c0, vr->hi, vr->pair_c, vr->bfx, vr->bfy, vr->bfz};
 #else
-    const TriRegs g = {a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c};
+    const TriRegs g = {a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c, fsub(t.hfx, 0.5f), fsub(t.hfy, 0.5f), fsub(t.hfz, 0.5f)};
 #endif
     Counters cnt = {0, 0, 0, 0, 0};
     for (;;) {
@@ -237,7 +364,7 @@ __global__ void __launch_bounds__(kCtaThreads, SHADE ? 0 : 6) tri_kernel(const _
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
         if (col < a.width && row < a.height) {
-            const uint32_t rgba = cast_ray_tri<COUNT, FAST, SHADE>(a, t, g, s_esl, col, row, cnt);
+            const uint32_t rgba = cast_ray_tri<COUNT, FAST, SHADE, FMA>(a, t, g, s_esl, col, row, cnt);
             if (!COUNT) {
                 const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
                 reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;
