@@ -131,23 +131,29 @@ def test_gpu_trilinear_matches_restated_oracle(name, clamped, policy, golden, po
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("ctas", ["5", "4"])
-def test_gpu_trilinear_fma_register_budget_variants(ctas, golden, port, volumes, R, monkeypatch):
-    """The contracted unclamped march is built for three register budgets (VR5_TRIF_CTAS = 6 default, 5, 4): same bits."""
+@pytest.mark.parametrize("warp_fetch", [False, True])
+@pytest.mark.parametrize("ctas,depth", [("6", "1"), ("5", "1"), ("4", "1"), ("6", "2"), ("5", "2"), ("4", "2"), ("4", "3"), ("4", "4")])
+def test_gpu_trilinear_fma_budget_and_depth_variants(ctas, depth, warp_fetch, golden, port, volumes, R, monkeypatch):
+    """The contracted unclamped march is built for three register budgets (VR5_TRIF_CTAS = 6, 5, 4 CTAs per SM) and one to four
+    cell requests in flight per ray (VR5_TRIF_DEPTH), with the tile queue read per CTA or per warp: same bits every way."""
     monkeypatch.setenv("VR5_TRIF_CTAS", ctas)
-    case = next(c for c in golden["cases"] if c["name"] == "synthA64_semi_ortho")
-    sc = golden_scene(port, case, volumes(case["volume"]))
-    scene, params = product_scene(R, sc)
-    gpu = R.GPURenderer5(0, sampler="trilinear-fma")
-    try:
-        gpu.set_window_buffer(case["width"], case["height"])
-        gpu.set_scene(scene)
-        frame = gpu.render_volume(params)
-        want, _ = port.render(sc, trilinear="fma")
-        assert_parity(frame, want, exact=True, what=ctas)
-        assert gpu.last_variant() == 19
-    finally:
-        gpu.close()
+    monkeypatch.setenv("VR5_TRIF_DEPTH", depth)
+    if warp_fetch:
+        monkeypatch.setenv("VR5_WARP_FETCH", "1")
+    for name in ["synthA64_semi_ortho", "synthA64_semi_persp"]:
+        case = next(c for c in golden["cases"] if c["name"] == name)
+        sc = golden_scene(port, case, volumes(case["volume"]))
+        scene, params = product_scene(R, sc)
+        gpu = R.GPURenderer5(0, sampler="trilinear-fma")
+        try:
+            gpu.set_window_buffer(case["width"], case["height"])
+            gpu.set_scene(scene)
+            frame = gpu.render_volume(params)
+            want, _ = port.render(sc, trilinear="fma")
+            assert_parity(frame, want, exact=True, what=(name, ctas, depth))
+            assert gpu.last_variant() == 19
+        finally:
+            gpu.close()
 
 
 @pytest.mark.gpu

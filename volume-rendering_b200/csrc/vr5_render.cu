@@ -810,17 +810,25 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
         // variants: instrumented (clamped, shading code present), and {clamped, unclamped} x {shading code, none}
         const bool fused = r->sampler == VR5_SAMPLER_TRILINEAR_FMA;
         int v = (count ? 0 : 1 + (fast ? 2 : 0) + (shade ? 1 : 0)) + (fused ? 5 : 0);
-        if (v == 8) {  // contracted, unclamped, no shading code: register budget knob (default from profiles/r01_sampler_choice.md)
-            const char *env = getenv("VR5_TRIF_CTAS");
-            const int want = env ? atoi(env) : 6;
-            v = want == 5 ? 10 : want == 4 ? 11 : 8;
+        int depth = 1;
+        if (v == 8) {  // contracted, unclamped, no shading code: register budget x requests in flight (profiles/r01_sampler_choice.md)
+            const char *ec = getenv("VR5_TRIF_CTAS"), *ed = getenv("VR5_TRIF_DEPTH");
+            const int ctas = ec ? atoi(ec) : 6;
+            depth = ed ? atoi(ed) : 1;
+            if (depth < 1 || depth > 4) depth = 1;
+            // DEPTH requests run DEPTH steps past the clip interval: all of them must stay inside the guard cells
+            if (depth > 1 && !reach_ok(a, (float)(kTriGuard - 2) / (float)depth)) depth = 1;
+            static const int table[3][4] = {{8, 12, 12, 12}, {10, 13, 13, 13}, {11, 14, 15, 16}};  // rows: 6 / 5 / 4 CTAs per SM, columns: depth 1..4
+            v = table[ctas == 5 ? 1 : ctas == 4 ? 2 : 0][depth - 1];
         }
-        void (*const kernels[12])(const KArgs, const TriArgs) = {
+        void (*const kernels[17])(const KArgs, const TriArgs) = {
             tri_kernel<true, false, true, false>, tri_kernel<false, false, false, false>, tri_kernel<false, false, true, false>,
             tri_kernel<false, true, false, false>, tri_kernel<false, true, true, false>,
             tri_kernel<true, false, true, true>, tri_kernel<false, false, false, true>, tri_kernel<false, false, true, true>,
             tri_kernel<false, true, false, true>, tri_kernel<false, true, true, true>,
-            tri_kernel<false, true, false, true, 5>, tri_kernel<false, true, false, true, 4>};
+            tri_kernel<false, true, false, true, 5>, tri_kernel<false, true, false, true, 4>,
+            tri_kernel<false, true, false, true, 6, 2>, tri_kernel<false, true, false, true, 5, 2>, tri_kernel<false, true, false, true, 4, 2>,
+            tri_kernel<false, true, false, true, 4, 3>, tri_kernel<false, true, false, true, 4, 4>};
         int &per_sm = r->ctas_per_sm[500 + v];
         if (per_sm == 0) {
             e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernels[v], kCtaThreads, 0);

@@ -195,7 +195,7 @@ __device__ __forceinline__ void trif_classify(uint32_t pair_c, float v, float2 &
     cba = __ffma2_rn(both(w), make_float2(d.z, d.w), make_float2(a.z, a.w));
 }
 
-template <bool COUNT, bool FAST, bool SHADE, bool FMA>
+template <bool COUNT, bool FAST, bool SHADE, bool FMA, int DEPTH>
 __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, int col, int row,
                                                  Counters &cnt) {
     // View::get_ray, Raycaster::intersect and the leading empty-space loop are those of the nearest path (vr5_cast.cuh)
@@ -253,43 +253,56 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
     if (COUNT) cnt.rays_accum++;
     if (!(k <= k_far)) return 0u;
     if (FMA) {
-        // contracted march: accumulators and colours live in packed pairs (r,g) / (b,a)
+        // contracted march: accumulators and colours live in packed pairs (r,g) / (b,a). DEPTH cells are in flight per ray: the
+        // record of sample i + DEPTH is requested while sample i is interpolated (the kernel is bound by the latency of these
+        // loads - most warp-wide requests contain a DRAM miss - not by issue slots; profiles/r01_sampler_choice.md). The loop is
+        // unrolled DEPTH times so that every tap keeps its registers; each stage ends in ONE exit test, which keeps it a single
+        // basic block in which the scheduler places the request ahead of the arithmetic.
         float2 acc_rg = make_float2(0.0f, 0.0f), acc_ba = acc_rg;
         const float2 oxy = make_float2(ox, oy), dxy = make_float2(dx, dy), hfxy = make_float2(g.hfx, g.hfy), bfxy = make_float2(g.bfx, g.bfy);
-        TriTap2 tap = trif_request(t, g, px, py, pz);
-        bool more;
-        do {  // k <= k_far holds on entry (checked above); ONE exit test at the bottom keeps the body a single basic block, so the
-              // scheduler is free to issue the next cell's load ahead of this sample's arithmetic
+        TriTap2 taps[DEPTH];
+        float ka = k;  // k of the furthest requested sample; the same sequential k += step as the march itself
+        taps[0] = trif_request(t, g, px, py, pz);
+#pragma unroll
+        for (int j = 1; j < DEPTH; j++) {
+            ka = fadd(ka, step);
+            taps[j] = trif_request2<FAST>(t, g, __ffma2_rn(dxy, both(ka), oxy), __fmaf_rn(dz, ka, oz), hfxy, bfxy);
+        }
+        auto stage = [&](TriTap2 &tap) -> bool {  // consumes sample i from `tap`, refills it with sample i + DEPTH
             const float kn = fadd(k, step);
-            const float2 nxy = __ffma2_rn(dxy, both(kn), oxy);
-            const float nz = __fmaf_rn(dz, kn, oz);
-            const TriTap2 next = trif_request2<FAST>(t, g, nxy, nz, hfxy, bfxy);
+            ka = DEPTH > 1 ? fadd(ka, step) : kn;
             const float v = trif_resolve(tap);
+            tap = trif_request2<FAST>(t, g, __ffma2_rn(dxy, both(ka), oxy), __fmaf_rn(dz, ka, oz), hfxy, bfxy);
             float2 crg, cba;
             trif_classify(g.pair_c, v, crg, cba);
             if (COUNT) cnt.samples++;
-            if (SHADE) {
-                if (cba.y > a.shade_alpha) {
-                    const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
-                    const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
-                    const float inv = fdiv(1.0f, __fsqrt_rn(len2));
-                    const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
-                    const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
-                    const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
-                    const float vl = trif_resolve(trif_request(t, g, qx, qy, qz));
-                    const float diffuse = fmul(fmul(fsub(vl, v), kInv255), a.kd);
-                    crg = make_float2(fadd(crg.x, diffuse), fadd(crg.y, diffuse));
-                    cba.x = fadd(cba.x, diffuse);
-                    if (COUNT) cnt.shaded++;
-                }
-                px = nxy.x; py = nxy.y; pz = nz;
+            if (SHADE && cba.y > a.shade_alpha) {
+                const float px = __fmaf_rn(dx, k, ox), py = __fmaf_rn(dy, k, oy), pz = __fmaf_rn(dz, k, oz);  // the sample's own point
+                const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
+                const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
+                const float inv = fdiv(1.0f, __fsqrt_rn(len2));
+                const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
+                const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
+                const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
+                const float vl = trif_resolve(trif_request(t, g, qx, qy, qz));
+                const float diffuse = fmul(fmul(fsub(vl, v), kInv255), a.kd);
+                crg = make_float2(fadd(crg.x, diffuse), fadd(crg.y, diffuse));
+                cba.x = fadd(cba.x, diffuse);
+                if (COUNT) cnt.shaded++;
             }
             const float2 tr2 = both(fsub(1.0f, acc_ba.y));
             acc_rg = __ffma2_rn(crg, tr2, acc_rg);
             acc_ba = __ffma2_rn(cba, tr2, acc_ba);
-            more = !(acc_ba.y > g.threshold) & (kn <= k_far);  // early ray termination (strict >), then while (k <= k_far)
-            k = kn; tap = next;
-        } while (more);
+            const bool more = !(acc_ba.y > g.threshold) & (kn <= k_far);  // early ray termination (strict >), then while (k <= k_far)
+            k = kn;
+            return more;
+        };
+        for (;;) {  // k <= k_far holds on entry (checked above)
+            bool more = true;
+#pragma unroll
+            for (int j = 0; j < DEPTH; j++) more = more && stage(taps[j]);
+            if (!more) break;
+        }
         return trunc_clamp(fmul(acc_rg.x, 256.0f), 255u) | (trunc_clamp(fmul(acc_rg.y, 256.0f), 255u) << 8) |
                (trunc_clamp(fmul(acc_ba.x, 256.0f), 255u) << 16) | (trunc_clamp(fmul(acc_ba.y, 256.0f), 255u) << 24);
     }
@@ -328,8 +341,9 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
 }
 
 // same persistent-warp / tile-queue skeleton as cast_kernel
-// MINB = resident CTAs per SM the register budget is cut for (0: none; 6 = 40 registers, 5 = 48, 4 = 64)
-template <bool COUNT, bool FAST, bool SHADE, bool FMA, int MINB = (SHADE ? 0 : 6)>
+// MINB = resident CTAs per SM the register budget is cut for (0: none; 6 = 40 registers, 5 = 48, 4 = 64); DEPTH = cell
+// requests in flight per ray (contracted march only)
+template <bool COUNT, bool FAST, bool SHADE, bool FMA, int MINB = (SHADE ? 0 : 6), int DEPTH = 1>
 __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
     __shared__ float4 s_pair[kTriPairs][2];
     __shared__ uint32_t s_esl[1024];
@@ -352,19 +366,26 @@ __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_con
     const TriRegs g = {a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c, fsub(t.hfx, 0.5f), fsub(t.hfy, 0.5f), fsub(t.hfz, 0.5f)};
 #endif
     Counters cnt = {0, 0, 0, 0, 0};
+    __shared__ unsigned s_q;
     for (;;) {
         unsigned q = 0;
-        if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;
-        q = __shfl_sync(0xffffffffu, q, 0);
+        if (a.cta_fetch) {  // a 32x8-pixel block per CTA: its 8 warps march through neighbouring cells in step and share L1 lines (cast_kernel)
+            __syncthreads();
+            if (threadIdx.x == 0) s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
+            __syncthreads();
+            q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
+        } else {
+            if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;
+            q = __shfl_sync(0xffffffffu, q, 0);
+        }
         if (q >= a.n_queue) break;
         const uint32_t group = q >> (kGroupLog2X + kGroupLog2Y), within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);
         const uint32_t tx = ((group % a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
         const uint32_t tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
-        if (tx >= a.tiles_x || tyl >= a.tile_rows_local) continue;
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
-        if (col < a.width && row < a.height) {
-            const uint32_t rgba = cast_ray_tri<COUNT, FAST, SHADE, FMA>(a, t, g, s_esl, col, row, cnt);
+        if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle
+            const uint32_t rgba = cast_ray_tri<COUNT, FAST, SHADE, FMA, DEPTH>(a, t, g, s_esl, col, row, cnt);
             if (!COUNT) {
                 const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
                 reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;
