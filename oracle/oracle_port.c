@@ -467,10 +467,13 @@ int orc_render_rows_trilinear(const vr5_raycaster *r, uint8_t *rgba8, int row0, 
  * restates the same policy with those contractions written out as fmaf() - one rounding per fused operation -
  * and with the filtering formulas in their fused form:
  *
- *   point:    p = fma(d, k, o) per axis (march loop AND leading empty-space loop); k += step sequentially.
- *   volume:   texel position t = fma(p, n/2, n/2 - 0.5)  (= (p+1)*0.5*n - 0.5 with ONE rounding; n/2 and
- *             n/2 - 0.5 are exact), cell floor(t), weight w = t - floor(t), neighbours clamped to [0, n-1],
- *             lerp x then y then z as fma(w, b - a, a) on the raw byte values -> v in [0, 255].
+ *   point:    p = fma(d, k, o) per axis (leading empty-space loop, shading); k += step sequentially.
+ *   volume:   the ray is carried into texel space ONCE: per axis dv = d * n/2 and ov = fma(o, n/2, n/2 - 0.5)
+ *             (texel position of a world point p is fma(p, n/2, n/2 - 0.5) = (p+1)*0.5*n - 0.5 with one rounding;
+ *             n/2 and n/2 - 0.5 are exact). A march sample sits at texel position t = fma(dv, k, ov); the shading
+ *             sample, a free world point, at fma(p, n/2, n/2 - 0.5). Cell floor(t), weight w = t - floor(t),
+ *             neighbours clamped to [0, n-1], lerp x then y then z as fma(w, b - a, a) on the raw byte values ->
+ *             v in [0, 255].
  *   TF:       position u = fma(v, RN(128/255), -0.5), entry floor(u), weight u - floor(u), entries clamped to
  *             [0, 127], per channel fma(w, b - a, a).
  *   shading:  guard and light vector as GPURenderer4.cu:41-51 in separate roundings (rare path), second fetch
@@ -488,10 +491,14 @@ static inline float lerp_fma(float a, float b, float w) {
     return fmaf(w, d, a);
 }
 
-static inline void tri_axis_fma(float p, uint32_t n, int64_t *i0, int64_t *i1, float *w) {
+/* texel position of a world coordinate */
+static inline float texel_of_world(float p, uint32_t n) {
     float half_n = (float)n * 0.5f;
     float bias = half_n - 0.5f;
-    float t = fmaf(p, half_n, bias);
+    return fmaf(p, half_n, bias);
+}
+
+static inline void tri_axis_fma(float t, uint32_t n, int64_t *i0, int64_t *i1, float *w) {
     float fl = floorf(t);
     *w = t - fl;
     int64_t a = (int64_t)fl, b = a + 1;
@@ -502,13 +509,13 @@ static inline void tri_axis_fma(float p, uint32_t n, int64_t *i0, int64_t *i1, f
     *i0 = a; *i1 = b;
 }
 
-/* trilinear value on the byte scale, [0, 255] */
-static inline float fetch_trilinear_fma(const vr5_model *m, float px, float py, float pz) {
+/* trilinear value on the byte scale, [0, 255], at texel position (tx, ty, tz) */
+static inline float fetch_trilinear_fma(const vr5_model *m, float tx, float ty, float tz) {
     int64_t x0, x1, y0, y1, z0, z1;
     float wx, wy, wz;
-    tri_axis_fma(px, m->dims.x, &x0, &x1, &wx);
-    tri_axis_fma(py, m->dims.y, &y0, &y1, &wy);
-    tri_axis_fma(pz, m->dims.z, &z0, &z1, &wz);
+    tri_axis_fma(tx, m->dims.x, &x0, &x1, &wx);
+    tri_axis_fma(ty, m->dims.y, &y0, &y1, &wy);
+    tri_axis_fma(tz, m->dims.z, &z0, &z1, &wz);
     const uint64_t sx = m->dims.x, sxy = (uint64_t)m->dims.x * m->dims.y;
 #define VOX(X, Y, Z) ((float)m->data[(uint64_t)(Z) * sxy + (uint64_t)(Y) * sx + (uint64_t)(X)])
     float c00 = lerp_fma(VOX(x0, y0, z0), VOX(x1, y0, z0), wx);
@@ -554,12 +561,18 @@ static void cast_pixel_trilinear_fma(const vr5_raycaster *r, uint8_t *rgba8, int
     }
     if (k > k_far) return;
     cnt->rays_accum++;
+    /* the ray in texel space */
+    const vr5_model *m = &r->volume;
+    float hnx = (float)m->dims.x * 0.5f, hny = (float)m->dims.y * 0.5f, hnz = (float)m->dims.z * 0.5f;
+    float dvx = d.x * hnx, dvy = d.y * hny, dvz = d.z * hnz;
+    float ovx = texel_of_world(o.x, m->dims.x), ovy = texel_of_world(o.y, m->dims.y), ovz = texel_of_world(o.z, m->dims.z);
     vr5_f4 acc = {0, 0, 0, 0};
     while (k <= k_far) {
-        float v = fetch_trilinear_fma(&r->volume, px, py, pz);
+        float v = fetch_trilinear_fma(m, fmaf(dvx, k, ovx), fmaf(dvy, k, ovy), fmaf(dvz, k, ovz));
         vr5_f4 cur = classify_linear_fma(r->transfer_fn, v);
         cnt->samples++;
         if (cur.w > 0.05f && r->light_kd > 0.01f) {
+            px = fmaf(d.x, k, o.x); py = fmaf(d.y, k, o.y); pz = fmaf(d.z, k, o.z);
             float lx = r->view.light_pos.x - px, ly = r->view.light_pos.y - py, lz = r->view.light_pos.z - pz;
             float xx = lx * lx, yy = ly * ly, zz = lz * lz;
             float s = xx + yy;
@@ -568,7 +581,7 @@ static void cast_pixel_trilinear_fma(const vr5_raycaster *r, uint8_t *rgba8, int
             float nx = lx * inv, ny = ly * inv, nz = lz * inv;
             float ox = nx * 0.01f, oy = ny * 0.01f, oz = nz * 0.01f;
             float qx = px + ox, qy = py + oy, qz = pz + oz;
-            float v_l = fetch_trilinear_fma(&r->volume, qx, qy, qz);
+            float v_l = fetch_trilinear_fma(m, texel_of_world(qx, m->dims.x), texel_of_world(qy, m->dims.y), texel_of_world(qz, m->dims.z));
             float diff = v_l - v;
             diff = diff * ORC_INV_255;
             diff = diff * r->light_kd;
@@ -579,7 +592,6 @@ static void cast_pixel_trilinear_fma(const vr5_raycaster *r, uint8_t *rgba8, int
         acc.x = fmaf(cur.x, t, acc.x); acc.y = fmaf(cur.y, t, acc.y); acc.z = fmaf(cur.z, t, acc.z); acc.w = fmaf(cur.w, t, acc.w);
         if (acc.w > r->ray_threshold) break;
         k += r->ray_step;
-        px = fmaf(d.x, k, o.x); py = fmaf(d.y, k, o.y); pz = fmaf(d.z, k, o.z);
     }
     uint8_t *px8 = rgba8 + 4 * ((size_t)row * r->view.dims.x + (size_t)col);
     px8[0] = (uint8_t)unit_to_index(acc.x, 256);

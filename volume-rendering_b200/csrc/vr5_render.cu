@@ -814,7 +814,7 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
         if (v == 8) {  // contracted, unclamped, no shading code: register budget x requests in flight (profiles/r01_sampler_choice.md)
             const char *ec = getenv("VR5_TRIF_CTAS"), *ed = getenv("VR5_TRIF_DEPTH");
             const int ctas = ec ? atoi(ec) : 6;
-            depth = ed ? atoi(ed) : 1;
+            depth = ed ? atoi(ed) : 2;  // 6 CTAs per SM x 2 requests in flight measured best (profiles/r01_sampler_choice.md)
             if (depth < 1 || depth > 4) depth = 1;
             // DEPTH requests run DEPTH steps past the clip interval: all of them must stay inside the guard cells
             if (depth > 1 && !reach_ok(a, (float)(kTriGuard - 2) / (float)depth)) depth = 1;
@@ -829,7 +829,7 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
             tri_kernel<false, true, false, true, 5>, tri_kernel<false, true, false, true, 4>,
             tri_kernel<false, true, false, true, 6, 2>, tri_kernel<false, true, false, true, 5, 2>, tri_kernel<false, true, false, true, 4, 2>,
             tri_kernel<false, true, false, true, 4, 3>, tri_kernel<false, true, false, true, 4, 4>};
-        int &per_sm = r->ctas_per_sm[500 + v];
+        int &per_sm = r->ctas_per_sm[480 + v];  // 480..496 (cast_kernel variants use 0..63)
         if (per_sm == 0) {
             e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernels[v], kCtaThreads, 0);
             if (e != cudaSuccess || per_sm < 1) per_sm = 1;

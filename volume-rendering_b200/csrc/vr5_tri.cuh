@@ -126,9 +126,8 @@ __device__ __forceinline__ float2 both(float v) { return make_float2(v, v); }
 template <bool FMA>
 __device__ __forceinline__ float ray_point(float o, float d, float k) { return FMA ? __fmaf_rn(d, k, o) : fadd(o, fmul(d, k)); }
 
-// one axis, fused: t = fma(p, n/2, n/2 - 0.5), cell floor(t), weight t - floor(t); returns the biased bits of RD(t + magic)
-__device__ __forceinline__ uint32_t trif_axis(float p, float hf, float bf, float &w) {
-    const float t = __fmaf_rn(p, hf, bf);
+// one axis: cell floor(t) and weight t - floor(t) of texel position t; returns the biased bits of RD(t + magic)
+__device__ __forceinline__ uint32_t trif_axis(float t, float &w) {
     const float tm = __fadd_rd(t, kTriMagic);
     w = fsub(t, fsub(tm, kTriMagic));
     return __float_as_uint(tm);
@@ -151,23 +150,20 @@ __device__ __forceinline__ void trif_load(const TriArgs &t, const TriRegs &g, ui
     }
 }
 
-// request with x and y packed (march loop) and all-scalar (first sample, shading sample)
+// request the cell record of texel position (txy, tz) and keep the three weights: x and y packed, z scalar
 struct TriTap2 { uint2 c; float2 wxy; float wz; };
 template <bool FAST>
-__device__ __forceinline__ TriTap2 trif_request2(const TriArgs &t, const TriRegs &g, float2 pxy, float pz, float2 hfxy, float2 bfxy) {
+__device__ __forceinline__ TriTap2 trif_request(const TriArgs &t, const TriRegs &g, float2 txy, float tz) {
     TriTap2 tap;
-    const float2 t2 = __ffma2_rn(pxy, hfxy, bfxy);
-    const float2 tm2 = __fadd2_rd(t2, both(kTriMagic));
-    tap.wxy = sub2(t2, __fadd2_rn(tm2, both(-kTriMagic)));
-    const uint32_t bz = trif_axis(pz, g.hfz, g.bfz, tap.wz);
+    const float2 tm2 = __fadd2_rd(txy, both(kTriMagic));
+    tap.wxy = sub2(txy, __fadd2_rn(tm2, both(-kTriMagic)));
+    const uint32_t bz = trif_axis(tz, tap.wz);
     trif_load(t, g, __float_as_uint(tm2.x), __float_as_uint(tm2.y), bz, FAST, tap.c);
     return tap;
 }
-__device__ __forceinline__ TriTap2 trif_request(const TriArgs &t, const TriRegs &g, float px, float py, float pz) {
-    TriTap2 tap;
-    const uint32_t bx = trif_axis(px, g.hfx, g.bfx, tap.wxy.x), by = trif_axis(py, g.hfy, g.bfy, tap.wxy.y), bz = trif_axis(pz, g.hfz, g.bfz, tap.wz);
-    trif_load(t, g, bx, by, bz, false, tap.c);
-    return tap;
+// texel position of a free world point (shading sample): fma(p, n/2, n/2 - 0.5) per axis; clamped request
+__device__ __forceinline__ TriTap2 trif_request_world(const TriArgs &t, const TriRegs &g, float px, float py, float pz) {
+    return trif_request<false>(t, g, make_float2(__fmaf_rn(px, g.hfx, g.bfx), __fmaf_rn(py, g.hfy, g.bfy)), __fmaf_rn(pz, g.hfz, g.bfz));
 }
 
 // trilinear value on the byte scale: x-lerps of the z0 / z1 face pairs packed, then y packed, then z
@@ -253,38 +249,41 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
     if (COUNT) cnt.rays_accum++;
     if (!(k <= k_far)) return 0u;
     if (FMA) {
-        // contracted march: accumulators and colours live in packed pairs (r,g) / (b,a). DEPTH cells are in flight per ray: the
-        // record of sample i + DEPTH is requested while sample i is interpolated (the kernel is bound by the latency of these
-        // loads - most warp-wide requests contain a DRAM miss - not by issue slots; profiles/r01_sampler_choice.md). The loop is
-        // unrolled DEPTH times so that every tap keeps its registers; each stage ends in ONE exit test, which keeps it a single
-        // basic block in which the scheduler places the request ahead of the arithmetic.
+        // contracted march: the ray is carried into texel space once (dv = d * n/2, ov = fma(o, n/2, n/2 - 0.5)), a sample sits
+        // at texel position fma(dv, k, ov); accumulators and colours live in packed pairs (r,g) / (b,a). DEPTH cells are in flight
+        // per ray: the record of sample i + DEPTH is requested while sample i is interpolated (the kernel is bound by the latency
+        // of these loads - most warp-wide requests contain a DRAM miss - as much as by issue slots; profiles/r01_sampler_choice.md).
+        // The loop is unrolled DEPTH times so that every tap and its k keep their registers; each stage ends in ONE exit test,
+        // which keeps it a single basic block in which the scheduler places the request ahead of the arithmetic.
         float2 acc_rg = make_float2(0.0f, 0.0f), acc_ba = acc_rg;
-        const float2 oxy = make_float2(ox, oy), dxy = make_float2(dx, dy), hfxy = make_float2(g.hfx, g.hfy), bfxy = make_float2(g.bfx, g.bfy);
+        const float2 dvxy = make_float2(fmul(dx, g.hfx), fmul(dy, g.hfy)), ovxy = make_float2(__fmaf_rn(ox, g.hfx, g.bfx), __fmaf_rn(oy, g.hfy, g.bfy));
+        const float dvz = fmul(dz, g.hfz), ovz = __fmaf_rn(oz, g.hfz, g.bfz);
         TriTap2 taps[DEPTH];
-        float ka = k;  // k of the furthest requested sample; the same sequential k += step as the march itself
-        taps[0] = trif_request(t, g, px, py, pz);
+        float ks[DEPTH];  // ks[j] = k of the sample held in taps[j]: the same sequential k += step as the march itself
+        ks[0] = k;
+        taps[0] = trif_request<false>(t, g, __ffma2_rn(dvxy, both(k), ovxy), __fmaf_rn(dvz, k, ovz));
 #pragma unroll
         for (int j = 1; j < DEPTH; j++) {
-            ka = fadd(ka, step);
-            taps[j] = trif_request2<FAST>(t, g, __ffma2_rn(dxy, both(ka), oxy), __fmaf_rn(dz, ka, oz), hfxy, bfxy);
+            ks[j] = fadd(ks[j - 1], step);
+            taps[j] = trif_request<FAST>(t, g, __ffma2_rn(dvxy, both(ks[j]), ovxy), __fmaf_rn(dvz, ks[j], ovz));
         }
-        auto stage = [&](TriTap2 &tap) -> bool {  // consumes sample i from `tap`, refills it with sample i + DEPTH
-            const float kn = fadd(k, step);
-            ka = DEPTH > 1 ? fadd(ka, step) : kn;
+        // consumes sample i (tap, k = kc) and refills the tap with sample i + DEPTH, whose k follows that of sample i + DEPTH - 1
+        auto stage = [&](TriTap2 &tap, float &kc, const float k_last) -> bool {
+            const float ka = fadd(k_last, step);
             const float v = trif_resolve(tap);
-            tap = trif_request2<FAST>(t, g, __ffma2_rn(dxy, both(ka), oxy), __fmaf_rn(dz, ka, oz), hfxy, bfxy);
+            tap = trif_request<FAST>(t, g, __ffma2_rn(dvxy, both(ka), ovxy), __fmaf_rn(dvz, ka, ovz));
             float2 crg, cba;
             trif_classify(g.pair_c, v, crg, cba);
             if (COUNT) cnt.samples++;
             if (SHADE && cba.y > a.shade_alpha) {
-                const float px = __fmaf_rn(dx, k, ox), py = __fmaf_rn(dy, k, oy), pz = __fmaf_rn(dz, k, oz);  // the sample's own point
+                const float px = __fmaf_rn(dx, kc, ox), py = __fmaf_rn(dy, kc, oy), pz = __fmaf_rn(dz, kc, oz);  // the sample's world point
                 const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
                 const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
                 const float inv = fdiv(1.0f, __fsqrt_rn(len2));
                 const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
                 const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
                 const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
-                const float vl = trif_resolve(trif_request(t, g, qx, qy, qz));
+                const float vl = trif_resolve(trif_request_world(t, g, qx, qy, qz));
                 const float diffuse = fmul(fmul(fsub(vl, v), kInv255), a.kd);
                 crg = make_float2(fadd(crg.x, diffuse), fadd(crg.y, diffuse));
                 cba.x = fadd(cba.x, diffuse);
@@ -293,14 +292,18 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
             const float2 tr2 = both(fsub(1.0f, acc_ba.y));
             acc_rg = __ffma2_rn(crg, tr2, acc_rg);
             acc_ba = __ffma2_rn(cba, tr2, acc_ba);
-            const bool more = !(acc_ba.y > g.threshold) & (kn <= k_far);  // early ray termination (strict >), then while (k <= k_far)
-            k = kn;
-            return more;
+            kc = ka;
+            return !(acc_ba.y > g.threshold);  // early ray termination (strict >)
         };
-        for (;;) {  // k <= k_far holds on entry (checked above)
+        for (;;) {  // k <= k_far holds on entry (checked above); sample i + 1 marches on while (k <= k_far)
             bool more = true;
 #pragma unroll
-            for (int j = 0; j < DEPTH; j++) more = more && stage(taps[j]);
+            for (int j = 0; j < DEPTH; j++) {
+                if (more) {
+                    const bool open = stage(taps[j], ks[j], ks[(j + DEPTH - 1) % DEPTH]);
+                    more = open & (ks[(j + 1) % DEPTH] <= k_far);
+                }
+            }
             if (!more) break;
         }
         return trunc_clamp(fmul(acc_rg.x, 256.0f), 255u) | (trunc_clamp(fmul(acc_rg.y, 256.0f), 255u) << 8) |
