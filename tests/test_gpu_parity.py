@@ -163,6 +163,35 @@ def test_partition_pack_unpack(R, gpu, port, golden, volumes):
     gpu.set_partition(0, 1, False)
 
 
+@pytest.mark.parametrize("order", ["cols", "rings"])
+def test_queue_orders_cover_every_tile(order, R, gpu, port, golden, volumes, monkeypatch):
+    """The opt-in tile-queue orders (VR5_QUEUE_ORDER, build_group_order) are permutations of the row-major sweep: every pixel
+    is still rendered exactly once, whole frame and per-rank strips, on ragged window sizes."""
+    case = next(c for c in golden["cases"] if c["name"] == "synthA64_default_persp")  # 317 x 203: ragged
+    sc = golden_scene(port, case, volumes(case["volume"]))
+    scene, params = product_scene(R, sc)
+    w, h = case["width"], case["height"]
+    gpu.set_sampler("hybridw")
+    gpu.set_window_buffer(w, h)
+    gpu.set_scene(scene)
+    gpu.set_partition(0, 1, False)
+    whole = gpu.render_volume(params)
+    assert sha(whole) == case["frame_sha256"]
+    monkeypatch.setenv("VR5_QUEUE_ORDER", order)
+    try:
+        assert np.array_equal(gpu.render_volume(params), whole)
+        for world in (2, 3):
+            in_place = np.zeros((h, w, 4), dtype=np.uint8)
+            for rank in range(world):
+                gpu.set_partition(rank, world, False)
+                part = gpu.render_volume(params, out=in_place.copy())
+                own = (np.arange(h) // 4) % world == rank
+                in_place[own] = part[own]
+            assert np.array_equal(in_place, whole), (order, world)
+    finally:
+        gpu.set_partition(0, 1, False)
+
+
 def test_error_behaviour(R):
     """Reference conventions: 1 = failure, never exit (GPURenderer1.cu:86-112, cuda_utils.h:21-49)."""
     r = R.GPURenderer5(0)

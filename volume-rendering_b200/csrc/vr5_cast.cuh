@@ -90,7 +90,8 @@ struct KArgs {
                              // exactly n_queue + (number of warps in the grid) to it (each warp ends on one failed fetch),
                              // so the host knows the next base without touching the device (vr5_render.cu, launch)
     uint32_t n_queue;        // padded tile count
-    uint32_t tiles_x, tile_rows_local, groups_x;
+    uint32_t tiles_x, tile_rows_local, groups_x, groups_y;
+    const uint32_t *group_order;  // permutation of the groups (build_group_order) or NULL: row-major
     int cta_fetch;           // 1: a CTA takes 8 queue slots at a time (one barrier per block), 0: every warp takes its own
     Counters *counters;
 };
@@ -409,6 +410,17 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
            (trunc_clamp(fmul(ab, 256.0f), 255u) << 16) | (trunc_clamp(fmul(aa, 256.0f), 255u) << 24);
 }
 
+// Queue slot -> tile. Slots are handed out in groups of 4x8 tiles (32x32 px; neighbouring slots touch neighbouring voxels).
+// With a.group_order the groups are visited in the host's order (build_group_order in vr5_render.cu: opt-in orders that end
+// the launch on short rays; the default row-major sweep passes NULL).
+__device__ __forceinline__ void tile_of_slot(const KArgs &a, uint32_t q, uint32_t &tx, uint32_t &tyl) {
+    uint32_t group = q >> (kGroupLog2X + kGroupLog2Y);
+    const uint32_t within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);
+    if (a.group_order) group = __ldg(a.group_order + group);
+    tx = ((group % a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
+    tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
+}
+
 // ---- the kernel: persistent warps + atomic tile queue -----------------------------------------------------------------
 // SHADE=false is chosen by the host when no sample can take the shading path (light_kd <= 0.01 or no TF entry with
 // alpha > 0.05), CLAMP=false when the sampler is the padded 3-D texture and min_bound == (-1,-1,-1).
@@ -447,9 +459,8 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
             q = __shfl_sync(0xffffffffu, q, 0);
         }
         if (q >= a.n_queue) break;
-        const uint32_t group = q >> (kGroupLog2X + kGroupLog2Y), within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);
-        const uint32_t tx = ((group % a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
-        const uint32_t tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
+        uint32_t tx, tyl;
+        tile_of_slot(a, q, tx, tyl);
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
         if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle

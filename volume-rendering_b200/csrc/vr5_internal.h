@@ -75,6 +75,9 @@ struct vr5_renderer {
     uint8_t *hr_base = nullptr, *hr_dev = nullptr;  // host address / device alias of the page-locked block
     int hr_slots = 0;
     bool hr_registered = false;       // this handle page-locked the block (and un-registers it on detach)
+    // tile-queue group order (vr5_render.cu, build_group_order): device table and the geometry it was built for
+    uint32_t *d_group_order = nullptr;
+    uint32_t order_key[6] = {0, 0, 0, 0, 0, 0};  // width, height, rank, world, packed, mode
     // bookkeeping
     int ctas_per_sm[512] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;

@@ -10,6 +10,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -299,6 +300,7 @@ extern "C" void vr5_destroy(vr5_renderer *r) {
     vr5_hostring_detach(r);
     vr5_peer_close(r);
     free_layouts(r);
+    cudaFree(r->d_group_order);
     cudaFree(r->d_vol_linear);
     for (auto &ln : r->lanes) {
         cudaFree(ln.d_frame);
@@ -677,6 +679,55 @@ static cudaError_t launch_sc(vr5_renderer *r, const KArgs &a, bool count, bool s
     return shade ? launch_one<S, false, true, CL>(r, a) : launch_one<S, false, false, CL>(r, a);
 }
 
+// Order in which the tile queue hands out its 32x32-pixel groups. A persistent grid idles at the end of a launch behind its
+// last full-length tiles (a C3 tile is ~0.3 ms of one warp's time; ncu: SMs active 94 % of a lone launch), so a launch would
+// like to END on cheap tiles. Two orders that do were measured against the row-major sweep (profiles/r01_sampler_choice.md):
+// "cols" sweeps along the longer image side (its far end holds empty or short silhouette rays: the cube's projection never
+// exceeds 0.87 x the shorter side from the centre, ViewBase.cpp:49-55, :100-105); "rings" walks rings around the image centre
+// inside out. Both cut the tail of a LONE launch (trilinear-fma: 1.275 -> 1.224 ms with rings) and both lose in the overlapped
+// stream of frames, where the next frame fills the tail anyway and their wider working set costs L1/L2 hits (nearest: 0.561 ->
+// 0.577 / 0.582 ms per frame). Default therefore: row-major, no table; VR5_QUEUE_ORDER=cols|rings selects the others.
+static int queue_order_mode(const KArgs *a) {
+    const char *e = getenv("VR5_QUEUE_ORDER");
+    if (getenv("VR5_ROW_MAJOR") || (e && !strcmp(e, "rows"))) return 0;
+    if (e && !strcmp(e, "rings")) return 2;
+    if (e && !strcmp(e, "cols")) return 1;
+    (void)a;
+    return 0;
+}
+
+static int build_group_order(vr5_renderer *r, const KArgs *a, int mode) {
+    const uint32_t key[6] = {(uint32_t)a->width, (uint32_t)a->height, (uint32_t)r->rank, (uint32_t)r->world, (uint32_t)r->packed, (uint32_t)mode};
+    if (r->d_group_order && !memcmp(key, r->order_key, sizeof(key))) return 0;
+    const uint32_t n = a->groups_x * a->groups_y;
+    std::vector<uint32_t> order(n);
+    if (mode == 1) {
+        for (uint32_t gx = 0, i = 0; gx < a->groups_x; gx++)
+            for (uint32_t gy = 0; gy < a->groups_y; gy++) order[i++] = gy * a->groups_x + gx;
+    } else {
+        struct Item { int ring; float angle; uint32_t group; };
+        std::vector<Item> items(n);
+        const float gw = (float)(kTileW << kGroupLog2X);  // group width in pixels
+        for (uint32_t g = 0; g < n; g++) {
+            const uint32_t gx = g % a->groups_x, gy = g / a->groups_x;
+            const float cx = ((float)gx + 0.5f) * gw - 0.5f * (float)a->width;
+            // a group's local tile rows are strips of this rank: global row = (local tile row * world + rank) * kTileH
+            const float cy = (((float)gy + 0.5f) * (float)(1u << kGroupLog2Y) * (float)r->world + (float)r->rank) * (float)kTileH - 0.5f * (float)a->height;
+            items[g] = Item{(int)(sqrtf(cx * cx + cy * cy) / 64.0f), atan2f(cy, cx), g};
+        }
+        std::sort(items.begin(), items.end(), [](const Item &x, const Item &y) {
+            return x.ring != y.ring ? x.ring < y.ring : x.angle != y.angle ? x.angle < y.angle : x.group < y.group;
+        });
+        for (uint32_t i = 0; i < n; i++) order[i] = items[i].group;
+    }
+    sync_all(r);  // frames in flight may still read the previous table
+    if (r->d_group_order) { cudaFree(r->d_group_order); r->d_group_order = nullptr; }
+    VR5_CUDA(r, cudaMalloc(&r->d_group_order, (size_t)n * sizeof(uint32_t)));
+    VR5_CUDA(r, cudaMemcpy(r->d_group_order, order.data(), (size_t)n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    memcpy(r->order_key, key, sizeof(key));
+    return 0;
+}
+
 static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs *a) {
     if (!p) { vr5_fail(r, "vr5_render: NULL params", cudaSuccess, __FILE__, __LINE__); return 1; }
     // the reference's own guard (GPURenderer1.cu:101-102): volume, TF + ESL table, buffer
@@ -722,8 +773,13 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     a->tile_rows_local = (uint32_t)r->rank < strips ? (strips - r->rank + r->world - 1) / r->world : 0;
     a->cta_fetch = (!r->tf_opaque && !getenv("VR5_WARP_FETCH")) ? 1 : 0;
     a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
-    const uint32_t groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
-    a->n_queue = (a->groups_x * groups_y) << (kGroupLog2X + kGroupLog2Y);
+    a->groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
+    a->n_queue = (a->groups_x * a->groups_y) << (kGroupLog2X + kGroupLog2Y);
+    a->group_order = nullptr;
+    if (const int mode = a->n_queue ? queue_order_mode(a) : 0) {
+        if (build_group_order(r, a, mode)) return 1;
+        a->group_order = r->d_group_order;
+    }
     a->counters = reinterpret_cast<Counters *>(r->d_counters);
     return 0;
 }

@@ -382,9 +382,8 @@ __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_con
             q = __shfl_sync(0xffffffffu, q, 0);
         }
         if (q >= a.n_queue) break;
-        const uint32_t group = q >> (kGroupLog2X + kGroupLog2Y), within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);
-        const uint32_t tx = ((group % a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
-        const uint32_t tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
+        uint32_t tx, tyl;
+        tile_of_slot(a, q, tx, tyl);
         const int col = (int)tx * kTileW + (lane & 7);
         const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
         if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle
