@@ -513,6 +513,9 @@ def run_b200_arm(args, wl):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "peak_source": peak_src, "kernel": ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler.startswith("trilinear") else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant())),
                          "bytes_per_sample": voxel_bytes, "kernel_ms": float(k_ms.mean()),
+                         # the same algorithmic bytes over the time a frame takes in the timed loop, where the tail of one launch
+                         # overlaps the head of the next (frame lanes): the rate the workload is actually served at
+                         "achieved_in_stream": alg_bytes / (ms / args.steps * 1e-3) / 1e9, "frac_in_stream": alg_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
                          "kernel_ms_l2_flushed": float(k_ms_flushed.mean()), "algorithmic_bytes_per_launch": alg_bytes,
                          "note": ("trilinear policy, contracted arithmetic (GPURenderer4 semantics as nvcc -fmad=true builds them, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear-fma" else
                                   "trilinear policy (GPURenderer4 semantics, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear" else

@@ -98,15 +98,19 @@ __device__ __forceinline__ float tri_fetch(const TriArgs &t, const TriRegs &g, f
 // The shared table holds, for every f = floor(position) in [-1, 127], the pair (tf[clamp(f)], tf[clamp(f+1)] - tf[clamp(f)]):
 // no index clamps and no subtraction in the loop (the difference is the same RN subtraction, done once per CTA).
 constexpr int kTriPairs = 129;
-// pair_c = shared address of the table - ((bits(magic) - 1) << 5) (mod 2^32): the entry address is one shift-add of the bits
+// Two float4 tables, entries first and differences behind them (16-byte stride each: a quarter-warp's LDS.128 hits 8 different
+// bank groups for 8 consecutive entries; interleaved (entry, difference) pairs at a 32-byte stride gave 4 and ncu counted up to
+// 2.4 shared-memory bank conflicts per warp-sample on gradient-rich frames).
+constexpr int kTriDiffOffset = kTriPairs * 16;  // byte offset of the difference table
+// pair_c = shared address of the table - ((bits(magic) - 1) << 4) (mod 2^32): the entry address is one shift-add of the bits
 __device__ __forceinline__ float4 tri_classify(uint32_t pair_c, float s) {
     const float t = fsub(fmul(s, 128.0f), 0.5f);
     const float tm = __fadd_rd(t, kTriMagic);
     const float w = fsub(t, fsub(tm, kTriMagic));
-    const uint32_t addr = pair_c + (__float_as_uint(tm) << 5);
+    const uint32_t addr = pair_c + (__float_as_uint(tm) << 4);
     float4 a, d;
     asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(addr));
-    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr));
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr), "n"(kTriDiffOffset));
     return make_float4(fadd(a.x, fmul(w, d.x)), fadd(a.y, fmul(w, d.y)), fadd(a.z, fmul(w, d.z)), fadd(a.w, fmul(w, d.w)));
 }
 
@@ -133,6 +137,21 @@ __device__ __forceinline__ uint32_t trif_axis(float t, float &w) {
     return __float_as_uint(tm);
 }
 
+// the record load of the contracted march; experiment builds override it (L2 prefetch-size hints, tools/build_variant.sh)
+#ifndef VR5_TRIF_LDHINT
+#define VR5_TRIF_LDHINT 0
+#endif
+#if VR5_TRIF_LDHINT == 1
+#define VR5_TRIF_LD "ld.global.nc.L2::128B.v2.u32"
+#elif VR5_TRIF_LDHINT == 2
+#define VR5_TRIF_LD "ld.global.nc.L2::256B.v2.u32"
+#elif VR5_TRIF_LDHINT == 3
+#define VR5_TRIF_LD "ld.global.nc.L1::evict_last.v2.u32"
+#elif VR5_TRIF_LDHINT == 4
+#define VR5_TRIF_LD "ld.global.nc.L1::evict_last.L2::128B.v2.u32"
+#else
+#define VR5_TRIF_LD "ld.global.nc.v2.u32"
+#endif
 __device__ __forceinline__ void trif_load(const TriArgs &t, const TriRegs &g, uint32_t bx, uint32_t by, uint32_t bz, bool fast, uint2 &c) {
     if (fast) {
         uint32_t lo;
@@ -140,7 +159,7 @@ __device__ __forceinline__ void trif_load(const TriArgs &t, const TriRegs &g, ui
             : "=r"(lo) : "r"(bx), "r"(by), "r"(bz), "r"(g.s1), "r"(g.s2), "r"(g.c0));
         // volatile: the request stays where it is written, ahead of the current sample's arithmetic (ptxas otherwise sinks it below
         // the early-termination branch, to the end of the iteration, and the next iteration starts on its latency)
-        asm volatile("{\n\t.reg .u64 p;\n\tmov.b64 p, {%2, %3};\n\tld.global.nc.v2.u32 {%0, %1}, [p];\n\t}" : "=r"(c.x), "=r"(c.y) : "r"(lo), "r"(g.hi));
+        asm volatile("{\n\t.reg .u64 p;\n\tmov.b64 p, {%2, %3};\n\t" VR5_TRIF_LD " {%0, %1}, [p];\n\t}" : "=r"(c.x), "=r"(c.y) : "r"(lo), "r"(g.hi));
     } else {
         const int bias = (int)kTriMagicBits - 1 - kTriGuard;
         const uint32_t jx = (uint32_t)min(max((int)bx - bias, 0), (int)t.jx1);
@@ -183,10 +202,10 @@ __device__ __forceinline__ void trif_classify(uint32_t pair_c, float v, float2 &
     const float u = __fmaf_rn(v, kTfScale255, -0.5f);
     const float um = __fadd_rd(u, kTriMagic);
     const float w = fsub(u, fsub(um, kTriMagic));
-    const uint32_t addr = pair_c + (__float_as_uint(um) << 5);
+    const uint32_t addr = pair_c + (__float_as_uint(um) << 4);
     float4 a, d;
     asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(addr));
-    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr));
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr), "n"(kTriDiffOffset));
     crg = __ffma2_rn(both(w), make_float2(d.x, d.y), make_float2(a.x, a.y));
     cba = __ffma2_rn(both(w), make_float2(d.z, d.w), make_float2(a.z, a.w));
 }
@@ -348,17 +367,17 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
 // requests in flight per ray (contracted march only)
 template <bool COUNT, bool FAST, bool SHADE, bool FMA, int MINB = (SHADE ? 0 : 6), int DEPTH = 1>
 __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
-    __shared__ float4 s_pair[kTriPairs][2];
+    __shared__ float4 s_pair[2][kTriPairs];  // [0]: entries, [1]: differences to the next entry
     __shared__ uint32_t s_esl[1024];
     for (int i = threadIdx.x; i < kTriPairs; i += kCtaThreads) {
         const float4 lo = a.tf[min(max(i - 1, 0), 127)], hi = a.tf[min(i, 127)];
-        s_pair[i][0] = lo;
-        s_pair[i][1] = make_float4(fsub(hi.x, lo.x), fsub(hi.y, lo.y), fsub(hi.z, lo.z), fsub(hi.w, lo.w));
+        s_pair[0][i] = lo;
+        s_pair[1][i] = make_float4(fsub(hi.x, lo.x), fsub(hi.y, lo.y), fsub(hi.z, lo.z), fsub(hi.w, lo.w));
     }
     for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const uint32_t pair_c = (uint32_t)__cvta_generic_to_shared(&s_pair[0][0]) - ((kTriMagicBits - 1u) << 5);
+    const uint32_t pair_c = (uint32_t)__cvta_generic_to_shared(&s_pair[0][0]) - ((kTriMagicBits - 1u) << 4);
 #if VR5_TRI_PIN
     __shared__ TriRegs s_regs;
     if (threadIdx.x == 0) s_regs = TriRegs{a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c, fsub(t.hfx, 0.5f), fsub(t.hfy, 0.5f), fsub(t.hfz, 0.5f)};
