@@ -19,10 +19,14 @@ constexpr int kTileW = 8;
 constexpr int kTileH = 4;         // = strip height of the multi-GPU partition
 constexpr int kGroupLog2X = 2;    // default queue order: groups of 4x8 tiles (32x32 px) so neighbouring queue slots
 constexpr int kGroupLog2Y = 3;    //                      touch neighbouring voxels (L1/L2 locality)
-// Software-pipeline depth of the march loop: the voxel of sample i + 1 is requested before sample i is composited. A depth
-// of 2 was tried (C3: 0.630 ms against 0.616 ms at depth 1 - two register moves per iteration, no fewer long-scoreboard
-// stalls) and dropped; reach_ok() in vr5_render.cu scales the speculative reach with it.
-constexpr int kPrefetch = 1;
+// Software-pipeline depth of the march loop: the voxel of sample i + kPrefetch is requested before sample i is composited
+// (1 or 2; the launcher bounds the speculative reach with it, reach_ok() in vr5_render.cu). Depth 2 - two slots in an unrolled
+// loop, no register moves, 55 instead of 54 instructions per pair of samples, bit-identical frames - measured SLOWER on B200:
+// C3 0.585 against 0.561 ms per frame, C4 1.359 against 1.293 (profiles/r01_sampler_choice.md), so 1 stays the default.
+#ifndef VR5_PREFETCH
+#define VR5_PREFETCH 1
+#endif
+constexpr int kPrefetch = VR5_PREFETCH;
 constexpr int kWindowGuard = 8;   // guard voxels around the window layout (speculative prefetch reach, see window_ok)
 // 6 resident CTAs per SM (40 registers) measured best for the window variants (44 registers / 5 CTAs: 0.631 ms per C3 frame,
 // 40 / 6: 0.617, 36 / 7: 0.717 - profiles/r01_sampler_choice.md). 0 = no minimum for the others.
@@ -286,15 +290,14 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
     const f32x2 dxy = pack2(dx, dy), hxy = pack2(vs.hx, vs.hy), one2 = pack2(1.0f, 1.0f);
     constexpr int S0 = SAMPLER >= 3 ? 2 : SAMPLER;  // hybrids / window: first sample and shading samples come from the texture
-    uint32_t s = sample_volume<S0, CLAMP>(a, vs, px, py, pz);
-    // one march step; FETCH selects the memory path of the PREFETCHED voxel (2 = texture, 0 = linear / padded linear)
-    auto march = [&](auto fetch_tag) -> bool {
+    // voxel of the sample at ray parameter kq; FETCH selects the memory path (2 = texture, 0 = linear / padded linear, 4 = window,
+    // 5 / 6 = power-of-two window / texture). Speculative: kq may lie up to kPrefetch steps past k_far.
+    auto fetch = [&](auto fetch_tag, const float kq) -> uint32_t {
         constexpr int FETCH = decltype(fetch_tag)::value;
-        // next point: o + d*kn, then (p + 1) * (n/2) per axis; x,y packed, z scalar; packed products feed scalar adds
-        const float kn = fadd(k, step);
+        // point: o + d*kq, then (p + 1) * (n/2) per axis; x,y packed, z scalar; packed products feed scalar adds
         float mx, my;
-        unpack2(mul2(dxy, pack2(kn, kn)), mx, my);
-        const float nx = fadd(ox, mx), ny = fadd(oy, my), nz = fadd(oz, fmul(dz, kn));
+        unpack2(mul2(dxy, pack2(kq, kq)), mx, my);
+        const float nx = fadd(ox, mx), ny = fadd(oy, my), nz = fadd(oz, fmul(dz, kq));
         uint32_t sn;
         if (FETCH == 5 || FETCH == 6) {
             // power-of-two dims: (p + 1) * 2^e is exact, so floor((p + 1) * 2^e) + kP2Origin is read straight out of the
@@ -337,9 +340,28 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
             if (CLAMP) { ix = min(ix, a.nx1); iy = min(iy, a.ny1); iz = min(iz, a.nz1); }
             sn = (FETCH == 0 && !CLAMP) ? fetch_padded(a, ix, iy, iz) : fetch_voxel<(FETCH >= 4 ? 0 : FETCH)>(a, ix, iy, iz);
         }
-        float4 c = lut_fetch(lut_addr, s);  // lut[s] == transfer_fn[s / TF_RATIO]
+        return sn;
+    };
+    // kPrefetch voxels are in flight per ray: slot j holds the voxel value ss[j] of the sample at ks[j]. A stage classifies and
+    // composites the sample of one slot and refills the slot with the sample kPrefetch steps ahead, whose k follows that of the
+    // other slot (the same sequential k += step as the reference). The loop is unrolled so that every slot keeps its registers.
+    uint32_t ss[kPrefetch];
+    float ks[kPrefetch];
+    ss[0] = sample_volume<S0, CLAMP>(a, vs, px, py, pz);
+    ks[0] = k;
+#pragma unroll
+    for (int j = 1; j < kPrefetch; j++) {
+        ks[j] = fadd(ks[j - 1], step);
+        ss[j] = fetch(FetchTag<S0 == 2 ? (is_p2(SAMPLER) ? 6 : 2) : S0>(), ks[j]);
+    }
+    // one march step: returns true when the ray is finished
+    auto stage = [&](auto fetch_tag, uint32_t &s_cur, float &k_cur, const float k_last, const float &k_next) -> bool {
+        const float ka = fadd(k_last, step);
+        const uint32_t sn = fetch(fetch_tag, ka);
+        float4 c = lut_fetch(lut_addr, s_cur);  // lut[s] == transfer_fn[s / TF_RATIO]
         if (COUNT) cnt.samples++;
         if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
+            const float px = fadd(ox, fmul(dx, k_cur)), py = fadd(oy, fmul(dy, k_cur)), pz = fadd(oz, fmul(dz, k_cur));  // the sample's point
             const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
             const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
             const float inv = fdiv(1.0f, __fsqrt_rn(len2));
@@ -347,7 +369,7 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
             const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
             const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
             const uint32_t sl = sample_volume<S0, true>(a, vs, qx, qy, qz);  // may leave the cube: always clamped
-            const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s, 255.0f)), a.kd);
+            const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s_cur, 255.0f)), a.kd);
             c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
             if (COUNT) cnt.shaded++;
         }
@@ -358,25 +380,31 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
         unpack2(mul2(pack2(c.x, c.y), t2), qr, qg);
         unpack2(mul2(pack2(c.z, c.w), t2), qb, qa);
         ar = fadd(ar, qr); ag = fadd(ag, qg); ab = fadd(ab, qb); aa = fadd(aa, qa);
-        if (aa > threshold) return true;   // early ray termination, strict >
-        if (!(kn <= k_far)) return true;   // while (k <= k_far)
-        k = kn; px = nx; py = ny; pz = nz; s = sn;
-        return false;
+        s_cur = sn; k_cur = ka;
+        if (aa > threshold) return true;               // early ray termination, strict >
+        return !((kPrefetch > 1 ? k_next : ka) <= k_far);  // while (k <= k_far) for the NEXT sample
     };
+    // stage u of the unrolled loop works on slot u % kPrefetch; its fetch path follows the sampler's pattern
+#define VR5_STAGE(TAG, U) stage(FetchTag<TAG>(), ss[(U) % kPrefetch], ks[(U) % kPrefetch], ks[((U) + kPrefetch - 1) % kPrefetch], ks[((U) + 1) % kPrefetch])
     if (is_p2(SAMPLER)) {
         if (p2_mode(SAMPLER) == 0) {
             for (;;) {
-                if (march(FetchTag<6>())) break;
-                if (march(FetchTag<5>())) break;
+                if (VR5_STAGE(6, 0)) break;
+                if (VR5_STAGE(5, 1)) break;
             }
         } else if (p2_mode(SAMPLER) == 1) {
-            for (;;)
-                if (march(FetchTag<5>())) break;
+            for (;;) {
+                if (VR5_STAGE(5, 0)) break;
+                if (VR5_STAGE(5, 1)) break;
+            }
         } else {
             for (;;) {
-                if (march(FetchTag<6>())) break;
-                if (march(FetchTag<5>())) break;
-                if (march(FetchTag<5>())) break;
+                if (VR5_STAGE(6, 0)) break;
+                if (VR5_STAGE(5, 1)) break;
+                if (VR5_STAGE(5, 2)) break;
+                if (VR5_STAGE(6, 3)) break;
+                if (VR5_STAGE(5, 4)) break;
+                if (VR5_STAGE(5, 5)) break;
             }
         }
     } else if (SAMPLER == 3) {
@@ -384,27 +412,35 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs,
         // costs 8 TEX wavefronts, which made the texture pipe the limiter (79 % busy, profiles/r01_v3_*); 1:1 measured
         // best against 2:1 and 1:2 (0.647 / 0.706 / 0.716 ms per C3 frame).
         for (;;) {
-            if (march(FetchTag<2>())) break;
-            if (march(FetchTag<0>())) break;
+            if (VR5_STAGE(2, 0)) break;
+            if (VR5_STAGE(0, 1)) break;
         }
     } else if (SAMPLER == 4) {  // texture : window, 1 : 1
         for (;;) {
-            if (march(FetchTag<2>())) break;
-            if (march(FetchTag<4>())) break;
+            if (VR5_STAGE(2, 0)) break;
+            if (VR5_STAGE(4, 1)) break;
         }
     } else if (SAMPLER == 5) {  // window only
-        for (;;)
-            if (march(FetchTag<4>())) break;
+        for (;;) {
+            if (VR5_STAGE(4, 0)) break;
+            if (VR5_STAGE(4, 1)) break;
+        }
     } else if (SAMPLER == 6) {  // texture : window, 1 : 2
         for (;;) {
-            if (march(FetchTag<2>())) break;
-            if (march(FetchTag<4>())) break;
-            if (march(FetchTag<4>())) break;
+            if (VR5_STAGE(2, 0)) break;
+            if (VR5_STAGE(4, 1)) break;
+            if (VR5_STAGE(4, 2)) break;
+            if (VR5_STAGE(2, 3)) break;
+            if (VR5_STAGE(4, 4)) break;
+            if (VR5_STAGE(4, 5)) break;
         }
     } else {
-        for (;;)
-            if (march(FetchTag<S0>())) break;
+        for (;;) {
+            if (VR5_STAGE(S0, 0)) break;
+            if (VR5_STAGE(S0, 1)) break;
+        }
     }
+#undef VR5_STAGE
     // Raycaster::write_color (RaycasterBase.h:44-50)
     return trunc_clamp(fmul(ar, 256.0f), 255u) | (trunc_clamp(fmul(ag, 256.0f), 255u) << 8) |
            (trunc_clamp(fmul(ab, 256.0f), 255u) << 16) | (trunc_clamp(fmul(aa, 256.0f), 255u) << 24);

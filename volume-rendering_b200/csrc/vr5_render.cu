@@ -790,12 +790,12 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
 static bool reach_ok(const KArgs &a, float lim);
 static bool window_ok(const vr5_renderer *r, const KArgs &a) {
     if (!r->d_vol_window && !r->p2_wl) return false;
-    return reach_ok(a, (float)((r->p2_wl ? kP2Origin : kWindowGuard) - 2));
+    return reach_ok(a, (float)((r->p2_wl ? kP2Origin : kWindowGuard) - 2) / (float)kPrefetch);
 }
 
-// true when no prefetch of the frame (kPrefetch steps past the clip interval) can move more than `lim` voxels on any axis
+// true when no march step of the frame moves more than `lim` voxels on any axis (callers divide their guard margin by the
+// number of steps a speculative fetch may run past the clip interval)
 static bool reach_ok(const KArgs &a, float lim) {
-    lim /= (float)kPrefetch;
     const float hx = a.hx, hy = a.hy, hz = a.hz;
     if (!(a.step > 0.0f) || !std::isfinite(a.step)) return false;
     for (int c = 0; c < 4; c++) {
@@ -911,9 +911,9 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
         return 0;
     }
     switch (r->sampler) {
-        case VR5_SAMPLER_LINEAR: e = (cube && r->d_vol_padded && reach_ok(a, (float)(kWindowGuard - 2))) ? launch_sc<0, false>(r, a, count, shade) : launch_sc<0, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_LINEAR: e = (cube && r->d_vol_padded && reach_ok(a, (float)(kWindowGuard - 2) / (float)kPrefetch)) ? launch_sc<0, false>(r, a, count, shade) : launch_sc<0, true>(r, a, count, shade); break;
         case VR5_SAMPLER_BRICK: e = launch_sc<1, true>(r, a, count, shade); break;
-        case VR5_SAMPLER_HYBRID: e = (cube && r->d_vol_padded && reach_ok(a, (float)(kWindowGuard - 2))) ? launch_sc<3, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
+        case VR5_SAMPLER_HYBRID: e = (cube && r->d_vol_padded && reach_ok(a, (float)(kWindowGuard - 2) / (float)kPrefetch)) ? launch_sc<3, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         case VR5_SAMPLER_HYBRID_WINDOW: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<4, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         case VR5_SAMPLER_WINDOW: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<5, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
         case VR5_SAMPLER_HYBRID_WINDOW2: e = (cube && r->d_vol_window && window_ok(r, a)) ? launch_sc<6, false>(r, a, count, shade) : cube ? launch_sc<2, false>(r, a, count, shade) : launch_sc<2, true>(r, a, count, shade); break;
