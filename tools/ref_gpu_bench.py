@@ -41,7 +41,7 @@ def main():
     wl = bench.WORKLOADS[args.workload]
     so = os.path.join(ROOT, "oracle", "_ref", "libvolr_ref_gpu.so")
     if not os.path.exists(so):
-        print(json.dumps({"impl": "reference-gpu", "unavailable": "oracle/_ref/libvolr_ref_gpu.so not built (needs /root/reference at build time)"}))
+        bench.emit({"impl": "reference-gpu", "unavailable": "oracle/_ref/libvolr_ref_gpu.so not built (needs /root/reference at build time)"})
         return
     lib = C.CDLL(so)
     lib.refgpu_create.restype = C.c_void_p
@@ -106,7 +106,7 @@ def main():
                      "vs_gpurenderer5_last_frame": {"exact": rep["exact"], "within1": rep["within1"], "max_lsb": rep["max"], "differing_pixels": rep["differing"]}}
     line["gpurenderer5_serial_device"] = {"ms_per_frame": ours_ms, "fps": 1e3 / ours_ms, "gsamples_per_s": samples / (ours_ms * 1e-3) / 1e9,
                                           "speedup_over_renderer3": res[3][1] / ours_ms}
-    print(json.dumps(line))
+    bench.emit(line)  # importing bench points fd 1 at stderr (library banners); emit() writes to the real stdout
 
 
 if __name__ == "__main__":
