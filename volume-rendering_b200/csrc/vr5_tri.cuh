@@ -138,6 +138,9 @@ __device__ __forceinline__ uint32_t trif_axis(float t, float &w) {
 }
 
 // the record load of the contracted march; experiment builds override it (L2 prefetch-size hints, tools/build_variant.sh)
+#ifndef VR5_TRIF_PACKZU
+#define VR5_TRIF_PACKZU 1
+#endif
 #ifndef VR5_TRIF_LDHINT
 #define VR5_TRIF_LDHINT 0
 #endif
@@ -198,6 +201,15 @@ __device__ __forceinline__ float trif_resolve(const TriTap2 &tap) {
 }
 
 // linear TF on the byte-scale value: position fma(v, 128/255, -0.5), same pair table as tri_classify
+// entry bits(um) (biased floor of the TF position) and weight w -> the interpolated colour pairs
+__device__ __forceinline__ void trif_classify_at(uint32_t pair_c, uint32_t um_bits, float w, float2 &crg, float2 &cba) {
+    const uint32_t addr = pair_c + (um_bits << 4);
+    float4 a, d;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(addr));
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr), "n"(kTriDiffOffset));
+    crg = __ffma2_rn(both(w), make_float2(d.x, d.y), make_float2(a.x, a.y));
+    cba = __ffma2_rn(both(w), make_float2(d.z, d.w), make_float2(a.z, a.w));
+}
 __device__ __forceinline__ void trif_classify(uint32_t pair_c, float v, float2 &crg, float2 &cba) {
     const float u = __fmaf_rn(v, kTfScale255, -0.5f);
     const float um = __fadd_rd(u, kTriMagic);
@@ -290,9 +302,26 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &
         auto stage = [&](TriTap2 &tap, float &kc, const float k_last) -> bool {
             const float ka = fadd(k_last, step);
             const float v = trif_resolve(tap);
-            tap = trif_request<FAST>(t, g, __ffma2_rn(dvxy, both(ka), ovxy), __fmaf_rn(dvz, ka, ovz));
             float2 crg, cba;
-            trif_classify(g.pair_c, v, crg, cba);
+#if VR5_TRIF_PACKZU
+            if (DEPTH > 1 && FAST) {
+                // the z axis of the requested sample and the TF position of the current one run the same four operations: packed
+                // (with DEPTH > 1 the request has a whole stage of slack, so waiting for v costs it nothing)
+                const float2 zu = __ffma2_rn(make_float2(dvz, v), make_float2(ka, kTfScale255), make_float2(ovz, -0.5f));
+                const float2 zum = __fadd2_rd(zu, both(kTriMagic));
+                const float2 wzu = sub2(zu, __fadd2_rn(zum, both(-kTriMagic)));
+                const float2 txy = __ffma2_rn(dvxy, both(ka), ovxy);
+                const float2 tm2 = __fadd2_rd(txy, both(kTriMagic));
+                tap.wxy = sub2(txy, __fadd2_rn(tm2, both(-kTriMagic)));
+                tap.wz = wzu.x;
+                trif_load(t, g, __float_as_uint(tm2.x), __float_as_uint(tm2.y), __float_as_uint(zum.x), true, tap.c);
+                trif_classify_at(g.pair_c, __float_as_uint(zum.y), wzu.y, crg, cba);
+            } else
+#endif
+            {
+                tap = trif_request<FAST>(t, g, __ffma2_rn(dvxy, both(ka), ovxy), __fmaf_rn(dvz, ka, ovz));
+                trif_classify(g.pair_c, v, crg, cba);
+            }
             if (COUNT) cnt.samples++;
             if (SHADE && cba.y > a.shade_alpha) {
                 const float px = __fmaf_rn(dx, kc, ox), py = __fmaf_rn(dy, kc, oy), pz = __fmaf_rn(dz, kc, oz);  // the sample's world point
