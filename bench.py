@@ -24,8 +24,6 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 # stdout carries exactly one JSON line. Libraries write there too (NCCL's version banner at communicator creation, the
 # reference's Logger), so file descriptor 1 is pointed at stderr for the life of the process and the line goes to the saved one.
-if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE") and not os.environ.get("NCCL_DEBUG_FILE"):
-    os.environ["NCCL_DEBUG"] = "WARN"
 sys.stdout.flush()
 _JSON_FD = os.dup(1)
 os.dup2(2, 1)
@@ -117,12 +115,12 @@ class CpuReference:
     """Drives the reference's own CPURenderer (kind "reference") or, if oracle/_ref was not prebuilt, the restated
     oracle (kind "port") on host volumes. The only place bench.py executes anything under oracle/."""
 
-    def __init__(self, wl):
+    def __init__(self, wl, volume=None):
         import oracle
         self.oracle, self.wl = oracle, wl
         self.port = oracle.Port()
         n = wl["n"]
-        self.volume = self.port.synth_a(n, wl["seed"]) if wl["kind"] == 0 else self.port.synth_b(n, wl["seed"])
+        self.volume = volume if volume is not None else self.port.synth_a(n, wl["seed"]) if wl["kind"] == 0 else self.port.synth_b(n, wl["seed"])
         base = self.port.default_base_tf()
         self.base_tf = oracle.tf_semi(base, n) if wl["tf"] == "semi" else (oracle.tf_opaque(base) if wl["tf"] == "opaque" else base)
         self.kind = "reference" if os.path.exists(oracle.REF_SO) and n <= 1024 else "port"  # 32-bit index limit, SURVEY H3
@@ -231,6 +229,170 @@ def run_reference_arm(args, wl):
 
 
 # ---- this repo's arm ---------------------------------------------------------------------------------------------------
+def peer_slots(lanes):
+    """Frame ring of the device-resident path: a producer may run this many frames ahead of the consumer (the per-frame
+    API needs a multiple of the frame lanes)."""
+    return 8 if 8 % max(1, lanes) == 0 else 3 * lanes
+
+
+def sha256(a) -> str:
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+class Rig:
+    """One renderer set up for (workload, sampler) on this rank, with the frame ring of the device-resident path attached:
+    rank 0 owns the ring, the other ranks map it over CUDA IPC (world 1: the same ring, nobody to map it)."""
+
+    def __init__(self, ctx, wl, sampler, overlap):
+        R, dist = ctx["R"], ctx["dist"]
+        self.ctx, self.wl, self.sampler = ctx, wl, sampler
+        self.rank, self.world, self.dev = ctx["rank"], ctx["world"], ctx["dev"]
+        n, w, h = wl["n"], wl["w"], wl["h"]
+        self.gpu = gpu = R.GPURenderer5(ctx["local_rank"], sampler=sampler)
+        gpu.set_stream(ctx["stream"].cuda_stream)
+        if ctx.get("volume_file"):
+            self.volume_route = install_volume_from_file(ctx, gpu, ctx["volume_file"])
+            n = max(self.volume_route["dims"])
+        else:
+            gpu.synth_volume(wl["kind"], n, wl["seed"])          # replicated: every rank generates the same bytes
+            self.volume_route = None
+        bd, mm, bs = gpu.build_minmax_device()
+        base = {"semi": lambda: R.tf_semi(n), "opaque": R.tf_opaque, "default": R.default_base_tf}[wl["tf"]]()
+        tf = R.premultiply_tf(base)
+        dims = self.volume_route["dims"] if self.volume_route else (n, n, n)
+        self.scene = R.Scene(None, tf, R.build_esl_bits(tf, mm), bd, bs, R.default_ray_step(*dims))
+        gpu.set_transfer_fn(self.scene.tf, self.scene.esl_bits)
+        gpu.set_window_buffer(w, h)
+        gpu.set_overlap(overlap)
+        gpu.set_partition(self.rank, self.world, False)
+        self.slots = peer_slots(overlap)
+        box = [gpu.peer_create(self.slots) if self.rank == 0 else None]
+        if self.world > 1:
+            dist.broadcast_object_list(box, src=0)
+            if self.rank != 0:
+                gpu.peer_open(box[0], self.slots)
+            dist.barrier()
+        self.seq = 0
+
+    def params(self, i, steps):
+        R = self.ctx["R"]
+        _, ang = orbit_angles(i, steps)
+        return self.scene.params(R.camera(self.wl["w"], self.wl["h"], 0, ang, 2.0))
+
+    def barrier(self):
+        import torch
+        self.gpu.sync()
+        if self.world > 1:
+            self.ctx["dist"].barrier()
+        torch.cuda.synchronize(self.dev)
+
+    def sequence(self, frames, copy_dst=None):
+        """The device-resident hot path: every rank renders its strips of all `frames` with ONE persistent launch that
+        stores the pixels into rank 0's frame ring (NVLink peer stores for the other ranks, in-kernel hand-shake); rank 0
+        consumes the frames in order (wait for all arrivals, optional device copy, release). Asynchronous."""
+        self.gpu.peer_render_sequence(frames, self.seq)
+        if self.rank == 0:
+            self.gpu.peer_consume_sequence(self.seq, len(frames), copy_dst)
+        self.seq += len(frames)
+        self.gpu.join()          # the stream waits (on the device) for the consumer
+
+    def timed_sequence(self, frames, warm):
+        """W warm-up frames, then exactly len(frames) frames between two events on the launching stream, barrier and
+        device synchronisation on both sides; returns the max over ranks in ms."""
+        import torch
+        self.sequence(warm)
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.barrier()
+        launches0 = self.gpu.launch_count()
+        e0.record(self.ctx["stream"])
+        self.sequence(frames)
+        e1.record(self.ctx["stream"])
+        self.launches = self.gpu.launch_count() - launches0    # kernels of this library launched inside the timed region
+        self.barrier()
+        ms_local = e0.elapsed_time(e1)
+        t = torch.tensor([ms_local], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            self.ctx["dist"].all_reduce(t, op=self.ctx["dist"].ReduceOp.MAX)
+        return float(t[0]), ms_local
+
+    def count(self, frames):
+        """Work counters of this rank's strips (instrumented kernel, untimed), summed over ranks."""
+        import torch
+        counts = [self.gpu.count(p) for p in frames]
+        local = (sum(c["samples"] for c in counts), sum(c["shaded"] for c in counts))
+        tot = torch.tensor(local, dtype=torch.int64, device=self.dev)
+        if self.world > 1:
+            self.ctx["dist"].all_reduce(tot)
+        return local, (int(tot[0]), int(tot[1]))
+
+    def frames_alone(self, frames):
+        """rank 0: the frames rendered by this GPU alone through the blocking per-frame call (vr5_render, host buffer)."""
+        out = []
+        self.gpu.set_partition(0, 1, False)
+        try:
+            for p in frames:
+                out.append(self.gpu.render_volume(p))
+        finally:
+            self.gpu.set_partition(self.rank, self.world, False)
+        return out
+
+    def frames_through_ring(self, frames):
+        """All ranks: the frames through the sequence path; rank 0 returns them (copied out of the ring by the consumer)."""
+        import torch
+        w, h = self.wl["w"], self.wl["h"]
+        dst = torch.zeros((len(frames), h, w, 4), dtype=torch.uint8, device=self.dev) if self.rank == 0 else None
+        self.sequence(frames, dst.data_ptr() if self.rank == 0 else None)
+        self.barrier()
+        self.gpu.peer_status()
+        return [f for f in dst.cpu().numpy()] if self.rank == 0 else None
+
+    def close(self):
+        self.barrier()
+        self.gpu.close()
+
+
+def install_volume_from_file(ctx, gpu, path):
+    """--volume-file: rank 0 decodes the file (vr5_load_volume: PVM / DDS, 16 -> 8 bit quantiser), uploads it, and the
+    DEVICE buffer is broadcast to the other ranks over NCCL (volume replicated from rank 0); every rank
+    installs it with vr5_set_volume_device."""
+    import torch
+    R, dist, rank, world, dev = ctx["R"], ctx["dist"], ctx["rank"], ctx["world"], ctx["dev"]
+    dims = [0, 0, 0]
+    vol = None
+    if rank == 0:
+        vol = R.load_volume(path)
+        dims = [int(vol.shape[2]), int(vol.shape[1]), int(vol.shape[0])]
+    if world > 1:
+        dist.broadcast_object_list(dims, src=0)
+    buf = torch.empty(dims[0] * dims[1] * dims[2], dtype=torch.uint8, device=dev)
+    if rank == 0:
+        buf.copy_(torch.from_numpy(vol.reshape(-1)))
+    if world > 1:
+        dist.broadcast(buf, src=0)
+    torch.cuda.synchronize(dev)
+    gpu.set_volume_device(buf.data_ptr(), buf.numel(), dims[0], dims[1], dims[2])
+    return {"file": os.path.basename(path), "dims": tuple(dims), "sha256": sha256(gpu.get_volume((dims[2], dims[1], dims[0]))),
+            "route": "rank 0 vr5_load_volume -> device buffer -> %s -> vr5_set_volume_device" % ("NCCL broadcast" if world > 1 else "same device")}
+
+
+def oracle_rows_check(wl, params_list, frames, rows, ctx, volume=None):
+    """rank 0: `rows` of each frame against the CPU checker (the reference's own code when it is prebuilt and its 32-bit
+    indices suffice, else the restated port): max LSB difference, rows checked."""
+    cpu = CpuReference(wl, volume=volume)
+    worst, checked = 0, 0
+    for (ang, frame) in zip(params_list, frames):
+        sc = cpu.scene(ang)
+        out = np.zeros((wl["h"], wl["w"], 4), dtype=np.uint8)
+        spans = [(r, r + 1) for r in rows]
+        cpu.render_rows(sc, out, spans, os.cpu_count() or 1)
+        for r in rows:
+            worst = max(worst, int(np.abs(out[r].astype(np.int16) - frame[r].astype(np.int16)).max()))
+            checked += 1
+    return {"oracle_rows": checked, "max_lsb": worst, "oracle_kind": cpu.kind}
+
+
 def run_b200_arm(args, wl):
     import torch
     import torch.distributed as dist
@@ -250,55 +412,96 @@ def run_b200_arm(args, wl):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-
-    n, w, h = wl["n"], wl["w"], wl["h"]
-    gpu = R.GPURenderer5(local_rank, sampler=args.sampler)
     stream = torch.cuda.Stream(device=dev)  # a real (non-default) stream shared by the kernels, NCCL and the timing events
     torch.cuda.set_stream(stream)
-    gpu.set_stream(stream.cuda_stream)
-    gpu.synth_volume(wl["kind"], n, wl["seed"])          # replicated: every rank generates the same bytes
-    bd, mm, bs = gpu.build_minmax_device()
-    base = {"semi": lambda: R.tf_semi(n), "opaque": R.tf_opaque, "default": R.default_base_tf}[wl["tf"]]()
-    tf = R.premultiply_tf(base)
-    scene = R.Scene(None, tf, R.build_esl_bits(tf, mm), bd, bs, R.default_ray_step(n, n, n))
-    gpu.set_transfer_fn(scene.tf, scene.esl_bits)
-    gpu.set_window_buffer(w, h)
+    ctx = dict(R=R, dist=dist, rank=rank, world=world, local_rank=local_rank, dev=dev, stream=stream, volume_file=args.volume_file)
+    L = R.lib()
+    failures = []
 
-    def params_for(i, steps):
-        _, ang = orbit_angles(i, steps)
-        return scene.params(R.camera(w, h, 0, ang, 2.0))
+    n, w, h = wl["n"], wl["w"], wl["h"]
+    rig = Rig(ctx, wl, args.sampler, args.overlap)
+    gpu, lanes = rig.gpu, args.overlap
+    frames = [rig.params(i, args.steps) for i in range(args.steps)]
+    frame_angles = [orbit_angles(i, args.steps)[1] for i in range(args.steps)]
+    warm = [rig.params(i * 7 + 3, ORBIT_FRAMES) for i in range(max(args.warmup, 3))]
 
-    frames = [params_for(i, args.steps) for i in range(args.steps)]
-    warm = [params_for(i * 7 + 3, ORBIT_FRAMES) for i in range(max(args.warmup, 3))]
+    # -- work counters per frame (instrumented kernel, untimed) ------------------------------------------------------
+    (samples_local, shaded_local), (samples_total, shaded_total) = rig.count(frames)
 
-    # N > 1: "peer" = every rank's kernel stores its pixels straight into rank 0's frame ring over NVLink (fused render +
-    # gather, csrc/vr5_peer.cu); "nccl" = packed strips + dist.gather + unpack kernel (the plain-collective baseline)
-    gather = args.gather if world > 1 else "none"
-    lanes = 1 if gather == "nccl" else args.overlap   # the NCCL gather consumes each frame on the one torch stream
-    gpu.set_overlap(lanes)
-    gpu.set_partition(rank, world, world > 1 and gather == "nccl")
-    PEER_SLOTS = 2 * max(1, args.overlap)   # a multiple of the lanes; two uses of headroom per lane
-    if gather == "peer":
-        box = [gpu.peer_create(PEER_SLOTS) if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        if rank != 0:
-            gpu.peer_open(box[0], PEER_SLOTS)
-        dist.barrier()
-    seq = [0]
-    # end-to-end leg at N > 1: "host" = every rank copies its own strips into a frame ring in shared HOST memory over its
-    # own PCIe link (csrc/vr5_hostring.cu); "peer" = rank 0 copies the gathered frame from its HBM (one link for all)
-    e2e_gather = args.e2e_gather if (world > 1 and gather == "peer") else "same"
-    hseq, hrel, ring_mem, ring_name = [0], [0], None, None
-    hprof = [0.0, 0.0]
-    # The consumer learns of a delivery through host memory, later than a stream would, and a frame is only delivered after
-    # kernel + copy + flag: it trails the producers by RING_LAG frames (measured at N=8: lag 3 -> 6 300 FPS, 4 -> 8 100,
-    # >= 7 -> the device rate), in a ring of 3 x lanes slots (producer of frame j needs frame j - slots released).
-    RING_SLOTS = 3 * max(1, args.overlap)
-    RING_LAG = RING_SLOTS - max(1, args.overlap) - 1
-    if os.environ.get("VR5_RING_SLOTS"):   # experiment knobs
-        RING_SLOTS = int(os.environ["VR5_RING_SLOTS"])
-    if os.environ.get("VR5_RING_LAG"):
-        RING_LAG = int(os.environ["VR5_RING_LAG"])
+    # -- timed region: exactly K steps = ONE sequence launch per rank, device timed, max over ranks -------------------
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    ms, ms_local = rig.timed_sequence(frames, warm)
+    lt = torch.tensor([rig.launches], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(lt)
+    launches = int(lt[0])
+    # keep the same load running (untimed) until the clock sampler has seen >= 1 s of it; the number of repeats is derived
+    # from the reduced time, so every rank runs the same count (the ring needs equal frame sequences on all ranks)
+    for _ in range(int(max(0.0, 1.0 - ms / 1e3) / max(ms / 1e3, 1e-6)) + 1):
+        rig.sequence(frames)
+    rig.barrier()
+    clocks.stop()
+    gpu.peer_status()   # raises if any in-kernel or stream wait timed out
+
+    # -- the same frames through the per-frame API of round 1 (one launch per frame, frame lanes), for comparison ------
+    def per_frame_loop(fr):
+        for p in fr:
+            gpu.peer_render(p, rig.seq)
+            if rank == 0:
+                gpu.peer_wait(rig.seq)
+                gpu.peer_release(rig.seq)
+            rig.seq += 1
+        gpu.join()
+    per_frame_loop(warm)
+    rig.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    per_frame_loop(frames)
+    e1.record(stream)
+    rig.barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_frame_api = float(t[0])
+    gpu.peer_status()
+
+    # -- N > 1: the plain-collective baseline (packed strips -> dist.gather over NCCL -> unpack kernel on rank 0) ----------
+    nccl_ms = None
+    if world > 1:
+        rows_padded = max(L.vr5_strip_rows(h, r, world) for r in range(world))
+        packed = torch.empty((rows_padded, w, 4), dtype=torch.uint8, device=dev)
+        gathered = torch.empty((world, rows_padded, w, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
+        frame_dev = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
+        gpu.set_overlap(1)
+        gpu.set_partition(rank, world, True)
+
+        def nccl_loop(fr):
+            for p in fr:
+                gpu.render_device(p, packed.data_ptr(), blocking=False)
+                dist.gather(packed, list(gathered.unbind(0)) if rank == 0 else None, dst=0)
+                if rank == 0:
+                    gpu.unpack_strips(gathered.data_ptr(), rows_padded, world, frame_dev.data_ptr())
+        nccl_loop(warm)
+        rig.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        nccl_loop(frames)
+        e1.record(stream)
+        rig.barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        nccl_ms = float(t[0])
+        nccl_sha = sha256(frame_dev.cpu().numpy()) if rank == 0 else None   # last frame, for `verify`
+        gpu.set_partition(rank, world, False)
+        gpu.set_overlap(lanes)
+        del packed, gathered
+
+    # -- end to end: frames land in HOST memory ------------------------------------------------------------------------
+    e2e_gather = args.e2e_gather if world > 1 else "same"
+    RING_SLOTS = 3 * max(1, lanes)            # the consumer trails the producers by RING_LAG frames
+    RING_LAG = RING_SLOTS - max(1, lanes) - 1
+    ring_mem, ring_name = None, None
     if e2e_gather == "host":     # the ring must fit the node's shared memory, else fall back to rank 0's copy
         fits = [False]
         if rank == 0:
@@ -320,134 +523,6 @@ def run_b200_arm(args, wl):
         dist.barrier()
         if rank != 0:
             ring_mem = R.ring_memory(ring_name, nbytes, create=False)
-
-    L = R.lib()
-    rows_padded = max(L.vr5_strip_rows(h, r, world) for r in range(world))
-    frame_devs = [torch.empty((h, w, 4), dtype=torch.uint8, device=dev) for _ in range(lanes)]  # frames in flight differ
-    frame_dev = frame_devs[0]
-    packed = torch.empty((rows_padded, w, 4), dtype=torch.uint8, device=dev) if gather == "nccl" else None
-    gathered = torch.empty((world, rows_padded, w, 4), dtype=torch.uint8, device=dev) if (gather == "nccl" and rank == 0) else None
-    pinneds = [torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() for _ in range(lanes)] if rank == 0 else None
-    pinned = pinneds[0] if rank == 0 else None
-
-    def step_device(p):
-        """One frame, device resident: N=1 renders in place; N>1 renders this rank's strips, gathers them to rank 0
-        over NCCL and scatters them into the frame there. Everything is enqueued on one stream, no host sync."""
-        if world == 1:
-            gpu.render_device(p, frame_devs[seq[0] % lanes].data_ptr(), blocking=False)
-            seq[0] += 1
-        elif gather == "peer":
-            gpu.peer_render(p, seq[0])
-            if rank == 0:
-                gpu.peer_wait(seq[0])       # frame complete in the ring (a consumer would read it here)
-                gpu.peer_release(seq[0])
-            seq[0] += 1
-        else:
-            gpu.render_device(p, packed.data_ptr(), blocking=False)
-            dist.gather(packed, list(gathered.unbind(0)) if rank == 0 else None, dst=0)
-            if rank == 0:
-                gpu.unpack_strips(gathered.data_ptr(), rows_padded, world, frame_dev.data_ptr())
-
-    def step_e2e(p):
-        """The call a user makes: the frame lands in HOST memory (pinned), like renderers 1-2 of the reference. With one
-        lane the call blocks per frame; with frame overlap frame i is enqueued (kernel + D2H on its lane) and the host
-        then waits for frame i - lanes + 1, i.e. it receives every frame, in order, lanes - 1 frames behind."""
-        i = seq[0]
-        if world == 1 and lanes == 1:
-            gpu.render_to_pinned(p, pinned.data_ptr())
-        elif world == 1:
-            gpu.render_async_host(p, pinneds[i % lanes].data_ptr())
-            seq[0] += 1
-            if i >= lanes - 1:
-                gpu.sync_lane((i - (lanes - 1)) % lanes)
-        elif e2e_gather == "host":
-            j = hseq[0]
-            ta = time.perf_counter()
-            gpu.hostring_render(p, j)          # kernel + strided D2H of this rank's strips into the shared host frame
-            tb = time.perf_counter()
-            hseq[0] += 1
-            if rank == 0 and j >= RING_LAG:    # the consumer receives every frame, in order, RING_LAG frames behind
-                gpu.hostring_wait(hrel[0])     # all ranks' strips of that frame are in host memory
-                gpu.hostring_release(hrel[0])
-                hrel[0] += 1
-            tc = time.perf_counter()
-            hprof[0] += tb - ta; hprof[1] += tc - tb
-        elif gather == "peer":
-            gpu.peer_render(p, i)
-            if rank == 0:
-                gpu.peer_wait(i)
-                gpu.peer_read(i, pinneds[i % lanes].data_ptr())   # D2H of the complete frame, on the frame's lane
-                gpu.peer_release(i)
-            seq[0] += 1
-            if i >= lanes - 1:
-                gpu.peer_sync_frame(i - (lanes - 1))
-        else:
-            step_device(p)
-            if rank == 0:
-                pinned.copy_(frame_dev, non_blocking=True)
-            stream.synchronize()
-
-    def barrier():
-        if world == 1:
-            gpu.set_overlap(lanes)   # every lane idle, next vr5_render* call on lane 0 ...
-            seq[0] += (-seq[0]) % lanes   # ... and this script's buffer index with it
-        else:
-            gpu.sync()               # peer frames keep their sequence: lane = seq % lanes, slot = seq % slots on every rank
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    # -- work counters per frame (instrumented kernel, untimed) ------------------------------------------------------
-    counts = [gpu.count(p) for p in frames]
-    samples_local = sum(c["samples"] for c in counts)
-    shaded_local = sum(c["shaded"] for c in counts)
-    tot = torch.tensor([samples_local, shaded_local], dtype=torch.int64, device=dev)
-    if world > 1:
-        dist.all_reduce(tot)
-    samples_total, shaded_total = int(tot[0]), int(tot[1])
-
-    # -- warm-up -------------------------------------------------------------------------------------------------
-    for p in warm:
-        step_device(p)
-    barrier()
-
-    # -- timed region: exactly K steps, device timed, max over ranks -----------------------------------------------
-    clocks = ClockSampler(local_rank)
-    launches0 = gpu.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    clocks.start()
-    barrier()
-    e0.record(stream)
-    for p in frames:
-        step_device(p)
-    gpu.join()           # the stream waits (on the device) for the last frame of every lane
-    e1.record(stream)
-    barrier()
-    ms = e0.elapsed_time(e1)
-    launches = gpu.launch_count() - launches0
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    lt = torch.tensor([launches], dtype=torch.int64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(lt)
-    ms = float(t[0])
-    launches = int(lt[0])
-    # keep the same load running (untimed) until the clock sampler has seen >= 1 s of it; the number of extra steps is
-    # derived from the reduced time, so every rank runs the same count (the peer ring needs equal frame sequences)
-    soak_steps = int(max(0.0, 1.0 - ms / 1e3) / max(ms / 1e3 / args.steps, 1e-6)) + 1
-    for i in range(soak_steps):
-        step_device(frames[i % len(frames)])
-    torch.cuda.synchronize(dev)
-    clocks.stop()
-
-    # -- end to end: host buffers, blocking call per frame, wall clock, max over ranks --------------------------------
-    def drain_host():
-        while rank == 0 and hrel[0] < hseq[0]:   # the last lanes - 1 frames
-            gpu.hostring_wait(hrel[0])
-            gpu.hostring_release(hrel[0])
-            hrel[0] += 1
-
-    if e2e_gather == "host":
         gpu.sync()
         gpu.set_partition(rank, world, True)     # packed strips for the strided copy
         if rank == 0:
@@ -456,18 +531,73 @@ def run_b200_arm(args, wl):
         if rank != 0:
             gpu.hostring_attach(ring_mem, RING_SLOTS, init=False)
         dist.barrier()
-    for p in warm[:3]:
-        step_e2e(p)
-    drain_host()
-    barrier()
+    pinneds = [torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() for _ in range(max(lanes, 1))] if rank == 0 else None
+    hseq, hrel = [0], [0]
+    host_frames = {}     # verification: frame index -> sha of what arrived in host memory
+
+    def e2e_loop(fr, keep=None):
+        """The pipelined host path: frame i is enqueued (kernel + D2H on its lane; N > 1: this rank's strips into the
+        shared host ring) and the host receives every frame, in order, a few frames behind."""
+        if world == 1:
+            gpu.set_overlap(lanes)
+            for i, p in enumerate(fr):
+                gpu.render_async_host(p, pinneds[i % lanes].data_ptr())
+                if i >= lanes - 1:
+                    gpu.sync_lane((i - (lanes - 1)) % lanes)
+                    if keep is not None:
+                        keep[i - (lanes - 1)] = sha256(pinneds[(i - (lanes - 1)) % lanes].numpy())
+            for i in range(max(0, len(fr) - (lanes - 1)), len(fr)):
+                gpu.sync_lane(i % lanes)
+                if keep is not None:
+                    keep[i] = sha256(pinneds[i % lanes].numpy())
+        elif e2e_gather == "host":
+            first = hseq[0]
+
+            def take():
+                ptr = gpu.hostring_wait(hrel[0])     # all ranks' strips of that frame are in host memory
+                if keep is not None:
+                    keep[hrel[0] - first] = sha256(np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(h, w, 4)))
+                gpu.hostring_release(hrel[0])
+                hrel[0] += 1
+            for p in fr:
+                gpu.hostring_render(p, hseq[0])      # kernel + strided D2H of this rank's strips into the shared host frame
+                hseq[0] += 1
+                if rank == 0 and hseq[0] - hrel[0] > RING_LAG:
+                    take()
+            while rank == 0 and hrel[0] < hseq[0]:
+                take()
+        else:   # rank 0 copies the frame gathered in its HBM
+            base = rig.seq
+            for p in fr:
+                i = rig.seq - base
+                gpu.peer_render(p, rig.seq)
+                if rank == 0:
+                    gpu.peer_wait(rig.seq)
+                    gpu.peer_read(rig.seq, pinneds[i % lanes].data_ptr())
+                    gpu.peer_release(rig.seq)
+                rig.seq += 1
+                if i >= lanes - 1:
+                    gpu.peer_sync_frame(rig.seq - lanes)
+                    if keep is not None and rank == 0:
+                        keep[i - (lanes - 1)] = sha256(pinneds[(i - (lanes - 1)) % lanes].numpy())
+            gpu.sync()
+            if keep is not None and rank == 0:
+                for i in range(max(0, len(fr) - (lanes - 1)), len(fr)):
+                    keep[i] = sha256(pinneds[i % lanes].numpy())
+
+    e2e_loop(warm[:3])
+    rig.barrier()
     t0 = time.perf_counter()
-    for p in frames:
-        step_e2e(p)
-    drain_host()
-    barrier()
+    e2e_loop(frames)
+    rig.barrier()
     e2e_s = time.perf_counter() - t0
-    if os.environ.get("VR5_BENCH_DEBUG"):
-        print("rank %d: e2e %.1f ms, in render calls %.1f ms, in wait/release %.1f ms" % (rank, e2e_s * 1e3, hprof[0] * 1e3, hprof[1] * 1e3), file=sys.stderr)
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t[0])
+    VERIFY_K = min(3, len(frames))
+    e2e_loop(frames[-VERIFY_K:], keep=host_frames)   # untimed: the frames the host path delivers, for `verify`
+    rig.barrier()
     if e2e_gather == "host":
         gpu.hostring_detach()
         gpu.set_partition(rank, world, False)
@@ -475,67 +605,208 @@ def run_b200_arm(args, wl):
         dist.barrier()
         if rank == 0:
             R.ring_memory_unlink(ring_name)
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_s = float(t[0])
 
-    # -- dominant kernel alone: per-launch CUDA events on its stream (this rank's share of each frame) ---------------
-    out_ptr = packed.data_ptr() if gather == "nccl" else frame_dev.data_ptr()
-    if gather == "peer":
-        gpu.peer_status()   # raises if any device-side wait timed out
-    k_ms = gpu.render_timed(frames, out_ptr, l2_flush=False)
-    k_ms_flushed = gpu.render_timed(frames[: min(len(frames), 24)], out_ptr, l2_flush=True)
+    # the blocking plugin call (what VolR.cpp:110 does: Renderer::render_volume(buffer, raycaster), host buffer, one frame per call)
+    e2e_blocking = None
+    if world == 1:
+        gpu.set_overlap(1)
+        host = np.empty((h, w, 4), dtype=np.uint8)
+        for p in warm[:3]:
+            gpu.render_volume(p, host)
+        t0 = time.perf_counter()
+        for p in frames:
+            gpu.render_volume(p, host)
+        blk_s = time.perf_counter() - t0
+        e2e_blocking = {"value": samples_total / blk_s / 1e9, "unit": UNIT, "fps": args.steps / blk_s, "ms_per_frame": 1e3 * blk_s / args.steps,
+                        "path": "vr5_render(handle, params, host pointer, out_is_device = 0): blocking, one frame per call, one lane, pageable host buffer - "
+                                "the call GPURenderer5::render_volume makes (VolR.cpp:110)"}
+        gpu.set_overlap(lanes)
+
+    # -- a single frame's launch alone (per-launch CUDA events on its stream): what one vr5_render call costs on the device ----
+    scratch = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
+    k_ms = gpu.render_timed(frames, scratch.data_ptr(), l2_flush=False)
+    k_ms_flushed = gpu.render_timed(frames[: min(len(frames), 24)], scratch.data_ptr(), l2_flush=True)
+    full_ms = None
+    if rank == 0 and world > 1:    # the whole frame on one GPU, for `ideal = full / N`
+        gpu.set_partition(0, 1, False)
+        full_ms = float(gpu.render_timed(frames, scratch.data_ptr(), l2_flush=False).mean())
+        gpu.set_partition(rank, world, False)
     strip_px = (L.vr5_strip_rows(h, rank, world) if world > 1 else h) * w
     voxel_bytes = 8.0 if args.sampler.startswith("trilinear") else 1.0   # nearest 1 B per fetch, trilinear 8 B
-    alg_bytes = voxel_bytes * (samples_local + shaded_local) / len(frames) + 4.0 * strip_px  # + 4 B per pixel written
+    alg_bytes_frame = voxel_bytes * (samples_local + shaded_local) / len(frames) + 4.0 * strip_px  # + 4 B per pixel written
+    alg_bytes_launch = alg_bytes_frame * len(frames)
     peak, peak_src = measured_peak()
-    achieved = alg_bytes / (float(k_ms.mean()) * 1e-3) / 1e9
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("%s_%s" % (args.workload, args.sampler))
-    except Exception:
-        pass
+    achieved = alg_bytes_launch / (ms_local * 1e-3) / 1e9
+    traffic, traffic_note = measured_traffic(args.workload, args.sampler, world, len(frames))
+
+    # -- verification (untimed): the frames of the timed paths against this GPU alone and against the CPU checker ------------
+    vparams, vangles = frames[-VERIFY_K:], frame_angles[-VERIFY_K:]
+    ring_frames = rig.frames_through_ring(vparams)
+    verify = None
+    if rank == 0:
+        alone = rig.frames_alone(vparams)
+        verify = {"frames": VERIFY_K,
+                  "sequence_frames_equal": sum(sha256(a) == sha256(b) for a, b in zip(alone, ring_frames)),
+                  "host_path_frames_equal": sum(host_frames.get(i) == sha256(a) for i, a in enumerate(alone)),
+                  "what": "sha256 of the last %d orbit frames: (sequence path through the frame ring%s) and (end-to-end host path: %s) against "
+                          "the same frames rendered by rank 0 alone with the blocking per-frame call" %
+                          (VERIFY_K, " over NVLink peer stores" if world > 1 else "", e2e_gather)}
+        if world > 1:
+            verify["nccl_gather_last_frame_equal"] = nccl_sha == sha256(alone[-1])
+            if not verify["nccl_gather_last_frame_equal"]:
+                failures.append("verify: NCCL gather frame differs")
+        if not args.volume_file:
+            rows = [int(r) for r in np.linspace(h // 4, 3 * h // 4, 16)]
+            verify.update(oracle_rows_check(wl, vangles[-1:], alone[-1:], rows, ctx))
+        if verify["sequence_frames_equal"] != VERIFY_K or verify["host_path_frames_equal"] != VERIFY_K or verify.get("max_lsb", 0) != 0:
+            failures.append("verify: %r" % verify)
 
     line = None
     if rank == 0:
         value = samples_total / (ms * 1e-3) / 1e9
+        kernel_name = ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler.startswith("trilinear") else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant()))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": len(warm),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "fps": args.steps / (ms * 1e-3),
-            "config": {"workload": wl["name"], "volume": "%d^3" % n, "viewport": "%dx%d" % (w, h), "tf": wl["tf"],
-                       "projection": "orthographic", "sampler": args.sampler, "frame_overlap_lanes": lanes, "samples_per_frame": samples_total / args.steps,
-                       "parallelism": ("image-space strips x%d, volume replicated, %s" % (world, "pixels stored straight into rank 0's frame ring over NVLink peer memory (fused render + gather)" if gather == "peer" else "NCCL gather to rank 0")) if world > 1 else "single GPU",
+            "ms_per_step_note": "time of the K-frame sequence launch / K: a throughput (all frames of the camera path in one persistent launch), not the latency of one frame; roofline.single_frame_launch_ms is the latter",
+            "config": {"workload": wl["name"] if not args.volume_file else "%s %s" % (rig.volume_route["file"], "x".join(map(str, rig.volume_route["dims"]))),
+                       "volume": "%d^3" % n, "viewport": "%dx%d" % (w, h), "tf": wl["tf"],
+                       "projection": "orthographic", "sampler": args.sampler, "samples_per_frame": samples_total / args.steps,
+                       "submission": "one persistent sequence launch per rank for all K frames (vr5_peer_render_sequence), frames consumed in order from a ring of %d device frames" % rig.slots,
+                       "parallelism": ("image-space strips x%d, volume replicated, pixels stored straight into rank 0's frame ring over NVLink peer memory (fused render + gather, hand-shake inside the kernel)" % world) if world > 1 else "single GPU",
                        "l2": "no flush in the timed loop: per frame the kernel reads the %.0f MB volume and writes the %.1f MB frame (L2 is 126 MB); "
-                             "the flushed per-kernel time is reported in roofline.kernel_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_src, "kernel": ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler.startswith("trilinear") else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant())),
-                         "bytes_per_sample": voxel_bytes, "kernel_ms": float(k_ms.mean()),
-                         # the same algorithmic bytes over the time a frame takes in the timed loop, where the tail of one launch
-                         # overlaps the head of the next (frame lanes): the rate the workload is actually served at
-                         "achieved_in_stream": alg_bytes / (ms / args.steps * 1e-3) / 1e9, "frac_in_stream": alg_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
-                         "kernel_ms_l2_flushed": float(k_ms_flushed.mean()), "algorithmic_bytes_per_launch": alg_bytes,
-                         "note": ("trilinear policy, contracted arithmetic (GPURenderer4 semantics as nvcc -fmad=true builds them, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear-fma" else
-                                  "trilinear policy (GPURenderer4 semantics, NOT the parity mode): 8 B per sample" if args.sampler == "trilinear" else
+                             "the flushed per-kernel time is reported in roofline.single_frame_launch_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
+                         "peak_source": peak_src, "kernel": kernel_name, "launch": "one launch = the K-frame sequence of the timed region (CUDA events on its stream)",
+                         "bytes_per_sample": voxel_bytes, "kernel_ms": ms_local, "frames_per_launch": len(frames), "algorithmic_bytes_per_launch": alg_bytes_launch,
+                         "single_frame_launch_ms": float(k_ms.mean()), "single_frame_launch_frac": alg_bytes_frame / (float(k_ms.mean()) * 1e-3) / 1e9 / peak,
+                         "single_frame_launch_ms_l2_flushed": float(k_ms_flushed.mean()),
+                         "note": ("trilinear policy, contracted arithmetic (GPURenderer4 semantics as nvcc -fmad=true builds them, NOT the CPURenderer parity mode): 8 B per sample" if args.sampler == "trilinear-fma" else
+                                  "trilinear policy (GPURenderer4 semantics, NOT the CPURenderer parity mode): 8 B per sample" if args.sampler == "trilinear" else
                                   "parity mode fetches 1 B per sample; the kernel is bound by the fp32 pipe and issue slots, not by HBM (DESIGN.md)")},
+            "per_frame_api": {"ms_per_step": ms_per_frame_api / args.steps, "value": samples_total / (ms_per_frame_api * 1e-3) / 1e9, "frame_overlap_lanes": lanes,
+                              "path": "round-1 submission: one launch per frame (vr5_peer_render + wait + release), frames round-robin over %d lanes" % lanes},
             "e2e": {"value": samples_total / e2e_s / 1e9, "unit": UNIT, "fps": args.steps / e2e_s, "h2d_bytes_per_step": C.sizeof(R.Params),
                     "d2h_bytes_per_step": w * h * 4,
-                    "path": {"host": "every rank copies its strips into a frame ring in shared host memory over its own PCIe link (vr5_hostring_*)",
-                             "peer": "rank 0 copies the frame gathered in its HBM (vr5_peer_read)", "same": "kernel + D2H of the frame on its lane"}[e2e_gather]},
+                    "path": {"host": "every rank copies its strips into a frame ring in shared host memory over its own PCIe link (vr5_hostring_*), %d lanes" % lanes,
+                             "peer": "rank 0 copies the frame gathered in its HBM (vr5_peer_read)",
+                             "same": "pipelined: vr5_render_async (kernel + D2H into pinned host memory on the frame's lane) with vr5_set_overlap(%d); the host receives every frame in order, %d frames behind" % (lanes, lanes - 1)}[e2e_gather]},
+            "verify": verify,
             "gpu_launches": launches, "clocks": clocks.summary(),
         }
+        if e2e_blocking:
+            line["e2e_blocking"] = e2e_blocking
+        if world > 1:
+            line["nccl_gather_baseline"] = {"ms_per_step": nccl_ms / args.steps, "value": samples_total / (nccl_ms * 1e-3) / 1e9,
+                                            "path": "packed strips, torch.distributed.gather over NCCL to rank 0, vr5_unpack_strips; serial frames on one stream"}
+            line["kernel_vs_ideal"] = {"single_frame_launch_ms_this_rank": float(k_ms.mean()), "full_frame_launch_ms_one_gpu": full_ms, "ideal_ms": full_ms / world,
+                                       "sequence_ms_per_frame": ms / args.steps}
+        if rig.volume_route:
+            line["volume_route"] = rig.volume_route
+    rig.close()
+
+    # -- the contracted trilinear policy (8 B per sample) in the same run: the row the HBM roofline is meaningful for -------
+    if world == 1 and not args.no_policies and not args.sampler.startswith("trilinear") and not args.volume_file:
+        rec = policy_record(ctx, wl, "trilinear-fma", args, peak)
+        if rank == 0:
+            line["policies"] = {"trilinear_fma": rec}
+    # -- C5 (2048^3, 7680x4320) in the same run: north_star's 1 -> 8 GPU scaling target is quoted on it --------------------
+    if not args.no_c5 and args.workload == "c3" and not args.volume_file:
+        rec = c5_record(ctx, args)
+        if rank == 0:
+            line["c5"] = rec
+            if rec.get("verify", {}).get("ok") is False:
+                failures.append("c5 verify: %r" % rec["verify"])
     if world > 1:
         dist.barrier()
     # -- CPU baseline next to it (rank 0, N=1 only): the reference's CPURenderer as shipped = 1 thread, one orbit frame ----
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not args.volume_file:
         line["cpu_baseline"] = cpu_baseline(args, wl)
     if rank == 0:
+        if failures:
+            line["failures"] = failures
         emit(line)
-    gpu.close()
     if world > 1:
         dist.destroy_process_group()
+    if failures:
+        raise SystemExit("bench.py: verification failed: " + "; ".join(failures))
+
+
+def measured_traffic(workload, sampler, world, frames_per_launch):
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed ncu capture of the SAME
+    (workload, sampler, GPUs) configuration: profiles/traffic.json holds bytes per FRAME of a sequence launch, keyed
+    "<workload>_<sampler>_n<gpus>". No capture for the configuration -> null with the reason (never another configuration's)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            per_frame = json.load(f).get("%s_%s_n%d" % (workload, sampler, world))
+    except Exception:
+        per_frame = None
+    if per_frame is None:
+        return None, "no ncu capture committed for (%s, %s, %d GPUs); ncu runs single-process only" % (workload, sampler, world)
+    return per_frame * frames_per_launch, "profiles/traffic.json: %.1f MB per frame (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of a sequence launch / its frames) x %d frames" % (per_frame / 1e6, frames_per_launch)
+
+
+def policy_record(ctx, wl, sampler, args, peak):
+    """Sub-record of another sampler policy on the same workload, measured like the headline (N = 1)."""
+    rig = Rig(ctx, wl, sampler, args.overlap)
+    frames = [rig.params(i, args.steps) for i in range(args.steps)]
+    warm = [rig.params(i * 7 + 3, ORBIT_FRAMES) for i in range(max(args.warmup, 3))]
+    (s_loc, sh_loc), (s_tot, sh_tot) = rig.count(frames)
+    ms, ms_local = rig.timed_sequence(frames, warm)
+    import torch
+    scratch = torch.empty((wl["h"], wl["w"], 4), dtype=torch.uint8, device=ctx["dev"])
+    k_ms = rig.gpu.render_timed(frames, scratch.data_ptr(), l2_flush=False)
+    alg_frame = 8.0 * (s_loc + sh_loc) / len(frames) + 4.0 * wl["w"] * wl["h"]
+    traffic, note = measured_traffic(args.workload, sampler, 1, len(frames))
+    rec = {"sampler": sampler, "ms_per_step": ms / len(frames), "value": s_tot / (ms * 1e-3) / 1e9, "unit": UNIT, "bytes_per_sample": 8.0,
+           "kernel": "vr5::tri_kernel<variant %d>" % rig.gpu.last_variant(), "kernel_ms": ms_local, "frames_per_launch": len(frames),
+           "achieved": alg_frame * len(frames) / (ms_local * 1e-3) / 1e9, "frac": alg_frame * len(frames) / (ms_local * 1e-3) / 1e9 / peak,
+           "single_frame_launch_ms": float(k_ms.mean()), "single_frame_launch_frac": alg_frame / (float(k_ms.mean()) * 1e-3) / 1e9 / peak,
+           "dram_bytes_measured": traffic, "dram_note": note,
+           "parity": TRILINEAR_PARITY_NOTE}
+    rig.close()
+    return rec
+
+
+TRILINEAR_PARITY_NOTE = ("NOT the CPURenderer parity mode. Pinned against the reference's GPURenderer4.cu compiled unmodified (texture references over texture objects, "
+                         "oracle/ref_gpu4_texobj.cu; hardware-filtered tex3D / tex1D) under the tolerance stated in tests/test_trilinear_pin.py; bit-equal to the restated "
+                         "fp32 checker, which an independent float64 restatement of the CUDA filtering formulas confirms (tests/test_trilinear_independent.py)")
+
+
+def c5_record(ctx, args):
+    """BASELINE.json configs[4]: synthA 2048^3 (8 GiB, replicated), 7680x4320, semi TF - a few orbit frames through the same
+    sequence path, every rank. north_star's >= 6x from 1 to 8 GPUs is quoted on this configuration."""
+    wl = WORKLOADS["c5"]
+    K = max(8, min(args.c5_frames, 64))
+    rig = Rig(ctx, wl, args.sampler, args.overlap)
+    frames = [rig.params(i, K) for i in range(K)]
+    angles = [orbit_angles(i, K)[1] for i in range(K)]
+    warm = [rig.params(i * 7 + 3, ORBIT_FRAMES) for i in range(3)]
+    (s_loc, sh_loc), (s_tot, sh_tot) = rig.count(frames)
+    ms, ms_local = rig.timed_sequence(frames, warm)
+    ring = rig.frames_through_ring(frames[-2:])
+    rec = None
+    if rig.rank == 0:
+        alone = rig.frames_alone(frames[-2:])
+        ver = {"frames": 2, "sequence_frames_equal": sum(sha256(a) == sha256(b) for a, b in zip(alone, ring))}
+        try:
+            with open("/proc/meminfo") as f:
+                avail_gib = next(int(l.split()[1]) for l in f if l.startswith("MemAvailable")) / 2 ** 20
+        except Exception:
+            avail_gib = 0.0
+        if rig.world == 1 and avail_gib > 28.0:   # CPU rows need the 8-GiB volume on the host: the bytes the kernel sees
+            vol = rig.gpu.get_volume((wl["n"],) * 3)
+            rows = [int(r) for r in np.linspace(wl["h"] // 4, 3 * wl["h"] // 4, 8)]
+            ver.update(oracle_rows_check(wl, angles[-1:], alone[-1:], rows, ctx, volume=vol))
+            del vol
+        else:
+            ver.update({"oracle_rows": 0, "oracle_note": "CPU rows at 2048^3 are checked at N = 1 with > 28 GiB of free host memory (and in tests/test_gpu_full_size.py)"})
+        ver["ok"] = ver["sequence_frames_equal"] == 2 and ver.get("max_lsb", 0) == 0
+        rec = {"workload": wl["name"], "n_frames": K, "ms_per_step": ms / K, "fps": K / (ms * 1e-3), "gsamples": s_tot / (ms * 1e-3) / 1e9,
+               "samples_per_frame": s_tot / K, "kernel": "vr5::cast_kernel<%s, variant %d>" % (args.sampler, rig.gpu.last_variant()), "verify": ver}
+    rig.close()
+    return rec
 
 
 def cpu_baseline(args, wl):
@@ -566,7 +837,10 @@ def main():
     ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2", "trilinear", "trilinear-fma"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap", type=int, default=4, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
-    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how strips reach rank 0")
+    ap.add_argument("--no-policies", action="store_true", help="skip the policies.trilinear_fma sub-record (N = 1)")
+    ap.add_argument("--no-c5", action="store_true", help="skip the c5 sub-record (2048^3 / 7680x4320)")
+    ap.add_argument("--c5-frames", type=int, default=8)
+    ap.add_argument("--volume-file", default=None, help="render a real dataset (.pvm): rank 0 decodes it, the device buffer is broadcast over NCCL")
     ap.add_argument("--e2e-gather", default="host", choices=["host", "peer"],
                     help="N > 1, end-to-end leg: host = every rank copies its strips into a shared host frame ring; peer = rank 0 copies the gathered frame")
     args = ap.parse_args()

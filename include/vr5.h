@@ -120,6 +120,15 @@ int vr5_render_raycaster(vr5_renderer *r, const vr5_raycaster *rc, void *out_rgb
 int vr5_render_async(vr5_renderer *r, const vr5_params *p, void *out_rgba8, int out_is_device);
 /* cudaStreamSynchronize on the renderer's stream and on every frame lane. */
 int vr5_sync(vr5_renderer *r);
+/* A whole camera path with ONE launch (the reference's benchmark loop calls render_volume once per frame, VolR.cpp:225-321):
+ * frames[0..n_frames) into the device buffers outs_dev[0..n_frames), asynchronously on the renderer's stream. The persistent
+ * grid pulls the tiles of ALL frames from one queue, so the launch has one tail however many frames it renders and the host
+ * pays one submission. The frames may differ in view.origin / direction / right_plane / up_plane only. Pixels are bit-equal
+ * to n_frames vr5_render calls. */
+int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev);
+/* Experiment knobs by name (the VR5_* environment variables vr5_create reads ONCE: VR5_QUEUE_ORDER = rows | cols | rings,
+ * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_WIN_SX). No effect on the pixels. */
+int vr5_set_option(vr5_renderer *r, const char *name, const char *value);
 /* Use an external stream (a cudaStream_t passed as void*, e.g. torch's current stream); NULL restores the own stream. */
 int vr5_set_stream(vr5_renderer *r, void *cuda_stream);
 /* Frame overlap. lanes = 1 (default): every frame runs on the renderer's stream, in order - the reference's behaviour.
@@ -169,9 +178,9 @@ int vr5_unpack_strips(vr5_renderer *r, const void *packed_all, uint32_t rows_pad
 /* The gathering rank ("owner") holds a ring of `slots` full frames plus flag words in one device allocation; every other
  * rank maps it (CUDA IPC) and its ray-cast kernel stores each pixel straight into its final place in the owner's frame
  * over NVLink. Frames carry a sequence number seq = 0, 1, 2, ... agreed by all ranks; frame seq lives in slot seq % slots.
- * Flags: arrive[slot] counts writer ranks that finished a frame in that slot; consumed[slot] = frames of it released.
- * A writer may store frame seq only after frame seq - slots was released; the owner may read frame seq only after all
- * world - 1 writers arrived. With frame overlap (vr5_set_overlap) frame seq runs on lane seq % lanes - slots must be a
+ * Flags: arrive[slot] counts ranks that finished their strips of a frame in that slot (the owner included); consumed[slot] =
+ * frames of it released. A rank may store frame seq only after frame seq - slots was released; the owner may read frame seq
+ * only after all `world` ranks arrived. With frame overlap (vr5_set_overlap) frame seq runs on lane seq % lanes - slots must be a
  * multiple of lanes - and vr5_peer_wait / read / release of a frame are enqueued on that frame's lane. Both conditions are enforced on the device by one-thread wait kernels (bounded: a wait
  * that exceeds the timeout sets a status flag instead of hanging). One process per GPU; never two ranks on one GPU. */
 #define VR5_PEER_HANDLE_BYTES 64
@@ -194,6 +203,15 @@ int vr5_peer_read(vr5_renderer *r, uint64_t seq, void *host_dst);
 int vr5_peer_release(vr5_renderer *r, uint64_t seq);
 /* any rank: block the host until everything enqueued for frame `seq` (render, wait, read, release) has finished */
 int vr5_peer_sync_frame(vr5_renderer *r, uint64_t seq);
+/* Frame sequences through the ring: every rank renders its strips of frames seq0 .. seq0 + n - 1 with ONE persistent launch
+ * (see vr5_render_sequence) on its renderer's stream. The hand-shake runs inside the kernel: a warp stores pixels of a frame
+ * only after the slot's previous frame was released, the warp that finishes the rank's last tile of a frame counts the
+ * rank's arrival. The owner calls it too, for its own strips. Asynchronous. */
+int vr5_peer_render_sequence(vr5_renderer *r, const vr5_params *frames, int n, uint64_t seq0);
+/* owner: consume frames seq0 .. seq0 + n - 1 in order on an internal stream (stream memory operations, no SM needed): wait
+ * for all ranks' arrivals of a frame, copy it device-to-device to copy_dst_dev + i * width * height * 4 if copy_dst_dev is
+ * not NULL, release its slot. Asynchronous; vr5_join orders the renderer's stream behind it, vr5_sync waits for it. */
+int vr5_peer_consume_sequence(vr5_renderer *r, uint64_t seq0, int n, void *copy_dst_dev);
 /* 0 = ok, 1 = some device-side wait timed out since vr5_peer_create / vr5_peer_open (synchronises the stream) */
 int vr5_peer_status(vr5_renderer *r);
 void vr5_peer_close(vr5_renderer *r);

@@ -20,6 +20,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 PORT_SO = os.path.join(HERE, "liboracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libvolr_ref.so")
+REF_GPU_SO = os.path.join(HERE, "_ref", "libvolr_ref_gpu.so")
 
 
 def build(quiet: bool = True) -> None:
@@ -335,6 +336,80 @@ class Ref:
     def render_rows(self, rc: Raycaster, out: np.ndarray, row0: int, row1: int) -> None:
         if self.lib.ref_render_rows(C.byref(rc), _u8p(out), row0, row1) != 0:
             raise RuntimeError("ref_render_rows returned 1")
+
+
+class RefGpu:
+    """_ref/libvolr_ref_gpu.so - the reference's own CUDA renderers 1-4 recompiled unmodified for sm_100a (renderer 4
+    through the texture-object shim of ref_gpu4_texobj.cu). Needs a GPU. The reference keeps its device state in statics
+    that its destructors free without clearing, so ONE instance lives per process (RefGpu.get) and scenes / windows are
+    changed through the reference's own set_* calls."""
+    _instance = None
+
+    @classmethod
+    def available(cls) -> bool:
+        return os.path.exists(REF_GPU_SO)
+
+    @classmethod
+    def get(cls, scene: Scene) -> "RefGpu":
+        if cls._instance is None:
+            cls._instance = cls(scene)
+        else:
+            cls._instance.set_scene(scene)
+        return cls._instance
+
+    def __init__(self, scene: Scene):
+        self.lib = C.CDLL(REF_GPU_SO)
+        L = self.lib
+        L.refgpu_create.restype = C.c_void_p
+        L.refgpu_create.argtypes = [C.POINTER(Raycaster)]
+        L.refgpu_run.argtypes = [C.c_void_p, C.c_int, C.POINTER(Raycaster), C.c_int, C.POINTER(C.c_uint8), C.POINTER(C.c_double)]
+        L.refgpu_set_scene.argtypes = [C.c_void_p, C.POINTER(Raycaster), C.c_int]
+        L.refgpu_set_window.argtypes = [C.c_void_p, C.POINTER(View)]
+        assert L.refgpu_sizeof_raycaster() == C.sizeof(Raycaster)
+        with _quiet_stdout():
+            self.h = L.refgpu_create(C.byref(scene.rc))
+        if not self.h:
+            raise RuntimeError("refgpu_create failed")
+        self.dims = (scene.width, scene.height)
+        self._scene = scene   # keeps the host arrays the POD points at alive
+
+    def set_scene(self, scene: Scene, volume_changed: bool = True):
+        with _quiet_stdout():
+            if (scene.width, scene.height) != self.dims:
+                if self.lib.refgpu_set_window(self.h, C.byref(scene.rc.view)) != 0:
+                    raise RuntimeError("refgpu_set_window failed")
+                self.dims = (scene.width, scene.height)
+            if self.lib.refgpu_set_scene(self.h, C.byref(scene.rc), 1 if volume_changed else 0) != 0:
+                raise RuntimeError("refgpu_set_scene failed")
+        self._scene = scene
+
+    def render(self, which: int, rcs) -> tuple[np.ndarray, float]:
+        """Frames rcs (one Raycaster or a list; all with this instance's window) through renderer `which` (1..4);
+        returns the LAST frame [H, W, 4] and the wall-clock ms of the loop."""
+        rcs = rcs if isinstance(rcs, (list, tuple)) else [rcs]
+        arr = (Raycaster * len(rcs))(*rcs)
+        out = np.zeros((self.dims[1], self.dims[0], 4), dtype=np.uint8)
+        ms = C.c_double()
+        with _quiet_stdout():
+            rc = self.lib.refgpu_run(self.h, which, arr, len(rcs), _u8p(out), C.byref(ms))
+        if rc != 0:
+            raise RuntimeError("refgpu_run(%d) returned %d" % (which, rc))
+        return out, float(ms.value)
+
+
+class _quiet_stdout:
+    """The reference's Logger prints to stdout; keep it out of JSON lines and test output."""
+
+    def __enter__(self):
+        import sys
+        sys.stdout.flush()
+        self.saved, self.null = os.dup(1), os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+
+    def __exit__(self, *exc):
+        os.dup2(self.saved, 1)
+        os.close(self.null)
+        os.close(self.saved)
 
 
 def ref_available() -> bool:

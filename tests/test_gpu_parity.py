@@ -177,7 +177,7 @@ def test_queue_orders_cover_every_tile(order, R, gpu, port, golden, volumes, mon
     gpu.set_partition(0, 1, False)
     whole = gpu.render_volume(params)
     assert sha(whole) == case["frame_sha256"]
-    monkeypatch.setenv("VR5_QUEUE_ORDER", order)
+    gpu.set_option("VR5_QUEUE_ORDER", order)   # the environment is read once, at vr5_create; later changes go through the ABI
     try:
         assert np.array_equal(gpu.render_volume(params), whole)
         for world in (2, 3):
@@ -189,7 +189,48 @@ def test_queue_orders_cover_every_tile(order, R, gpu, port, golden, volumes, mon
                 in_place[own] = part[own]
             assert np.array_equal(in_place, whole), (order, world)
     finally:
+        gpu.set_option("VR5_QUEUE_ORDER", "rows")
         gpu.set_partition(0, 1, False)
+
+
+@pytest.mark.parametrize("sampler", ["hybridw", "window", "linear", "hybrid", "tex3d", "trilinear", "trilinear-fma"])
+@pytest.mark.parametrize("perspective", [0, 1])
+def test_degenerate_view_keeps_the_clamps(sampler, perspective, port, R):
+    """the C ABI accepts any View bytes. A direction with an exactly-zero x component is fixed up to 1e-5 only
+    inside Raycaster::intersect (RaycasterBase.h:33-35); with the origin outside [-1, 1] on that axis and the other components
+    tiny, rays get a valid interval at k ~ 1e5 while every sample lies OUTSIDE the cube on x. The reference clamps the voxel
+    index (common.h:105-110); the unclamped kernel variants would form addresses far outside their guard margins. The launcher
+    must route such frames through the clamped variants: frames bit-equal to the CPU checker, no fault."""
+    rng = np.random.default_rng(3)
+    vol = rng.integers(1, 256, size=(64, 64, 64), dtype=np.uint8)
+    w, h = 64, 48
+    view = R.View()
+    view.dims[0], view.dims[1] = w, h
+    view.origin = R.F3(-2.0, 0.0, 0.0)
+    view.direction = R.F3(0.0, 1e-6, -1e-6)
+    view.right_plane = R.F3(0.004, 0.0, 0.0) if not perspective else R.F3(0.0, 1e-9, 0.0)
+    view.up_plane = R.F3(0.0, 0.01, 0.01) if not perspective else R.F3(0.0, 0.0, 1e-9)
+    view.light_pos = R.F3(0.0, 0.0, 3.0)
+    view.perspective = perspective
+    base = R.tf_semi(8)
+    tf = R.premultiply_tf(base)
+    bd, mm, bs = R.build_minmax(vol)
+    scene = R.Scene(vol, tf, R.build_esl_bits(tf, mm), bd, bs, 2.0e4, esl=False)
+    params = scene.params(view)
+    osc = port.make_scene(vol, oracle.tf_semi(port.default_base_tf(), 8), oracle.View.from_buffer_copy(bytes(view)), ray_step=2.0e4, esl=False)
+    mode = {"trilinear": True, "trilinear-fma": "fma"}.get(sampler, False)
+    want, cnt = port.render(osc, trilinear=mode)
+    assert cnt["samples"] > 1000 and want.max() > 0     # the degenerate rays do hit and do accumulate colour
+    g = R.GPURenderer5(0, sampler=sampler)
+    try:
+        g.set_window_buffer(w, h)
+        g.set_scene(scene)
+        frame = g.render_volume(params)
+        assert_parity(frame, want, exact=True, what=(sampler, perspective))
+        assert g.last_variant() in (0, 2, 16, 18), g.last_variant()   # linear / texture with clamps, clamped trilinear marches
+        assert g.count(params) == cnt
+    finally:
+        g.close()
 
 
 def test_error_behaviour(R):

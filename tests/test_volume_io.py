@@ -83,6 +83,14 @@ def test_pvm3_and_raw_and_errors(R, tmp_path):
         f.write(b"PVM\n4 3 2\n1\n" + vol.tobytes()[:-1])
     with pytest.raises(R.Vr5Error):
         R.load_pvm(bad)
+    # header fields whose product wraps modulo 2^64 (2^22 * 2^22 * 2^20 * 1 = 2^64 -> 0 voxels) must not pass
+    # the size check with a tiny buffer; neither must dimensions a ushort3 cannot hold
+    for hdr in (b"PVM\n4194304 4194304 1048576\n1\n", b"PVM\n65536 1 1\n1\n", b"PVM\n2 2 2\n5\n"):
+        huge = str(tmp_path / "huge.pvm")
+        with open(huge, "wb") as f:
+            f.write(hdr + bytes(64))
+        with pytest.raises(R.Vr5Error, match="65535"):
+            R.load_pvm(huge)
     three = str(tmp_path / "three.pvm")
     with open(three, "wb") as f:
         f.write(b"PVM\n2 2 2\n3\n" + bytes(24))

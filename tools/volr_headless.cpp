@@ -4,7 +4,11 @@
 // buffer through Renderer::render_volume, times each frame (wall clock around the blocking call, like Profiler method 0
 // but with a monotonic clock) and optionally dumps PPM images.
 //
-//   volr_headless [-n N] [-synth A|B] [-raw file dx dy dz] [-s W H] [-tf default|semi|opaque] [-ppm prefix] [-reps R]
+//   volr_headless [-n N] [-synth A|B] [-raw file dx dy dz] [-s W H] [-tf default|semi|opaque] [-ppm prefix] [-dump prefix]
+//                 [-device] [-reps R]
+// -device: the frame buffer is a cudaMalloc block, as the GL application hands renderers >= 3 the mapped pixel buffer
+//          (VolR.cpp:76-87); render_volume finds out by itself which kind of pointer it got (vr5_render, out_is_device = -1).
+// -dump:   raw RGBA8 frames, row 0 first, one file per pose (tests compare their sha256 with the reference's frames).
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -12,6 +16,8 @@
 #include <time.h>
 
 #include <vector>
+
+#include <cuda_runtime_api.h>
 
 #include "../include/vr5.h"
 #include "../volume-rendering_b200/csrc/GPURenderer5.h"
@@ -24,8 +30,8 @@ static double now_ms() {
 
 int main(int argc, char **argv) {
     int n = 256, w = 800, h = 600, reps = 3, synth = 0;
-    const char *tf_name = "default", *ppm = NULL, *raw = NULL;
-    int rdx = 0, rdy = 0, rdz = 0;
+    const char *tf_name = "default", *ppm = NULL, *raw = NULL, *dump = NULL;
+    int rdx = 0, rdy = 0, rdz = 0, device_buffer = 0;
     for (int i = 1; i < argc; i++) {
         if (!strcmp(argv[i], "-n") && i + 1 < argc) n = atoi(argv[++i]);
         else if (!strcmp(argv[i], "-synth") && i + 1 < argc) synth = argv[++i][0] == 'B';
@@ -34,7 +40,9 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "-tf") && i + 1 < argc) tf_name = argv[++i];
         else if (!strcmp(argv[i], "-ppm") && i + 1 < argc) ppm = argv[++i];
         else if (!strcmp(argv[i], "-reps") && i + 1 < argc) reps = atoi(argv[++i]);
-        else { fprintf(stderr, "usage: %s [-n N] [-synth A|B] [-raw file dx dy dz] [-s W H] [-tf default|semi|opaque] [-ppm prefix] [-reps R]\n", argv[0]); return 2; }
+        else if (!strcmp(argv[i], "-dump") && i + 1 < argc) dump = argv[++i];
+        else if (!strcmp(argv[i], "-device")) device_buffer = 1;
+        else { fprintf(stderr, "usage: %s [-n N] [-synth A|B] [-raw file dx dy dz] [-s W H] [-tf default|semi|opaque] [-ppm prefix] [-dump prefix] [-device] [-reps R]\n", argv[0]); return 2; }
     }
     // ---- volume on the host (ModelBase::volume) ----
     std::vector<uint8_t> vol;
@@ -84,6 +92,9 @@ int main(int argc, char **argv) {
     Renderer *renderer = new GPURenderer5(rc);  // VolR.cpp:425-429
     printf("renderer: %s\nvolume %dx%dx%d, viewport %dx%d, tf %s, ray_step %.6g\n", renderer->get_name(), dx, dy, dz, w, h, tf_name, rc.ray_step);
     std::vector<uint32_t> frame((size_t)w * h);
+    uchar4 *dev_frame = NULL;
+    if (device_buffer && cudaMalloc((void **)&dev_frame, frame.size() * 4) != cudaSuccess) { fprintf(stderr, "cudaMalloc frame buffer failed\n"); return 1; }
+    uchar4 *target = device_buffer ? dev_frame : reinterpret_cast<uchar4 *>(frame.data());
     const float poses[4][3] = {{0, 0, 0}, {-45, -45, 0}, {90, 0, 0}, {180, 90, 0}};  // VolR.cpp:235-244
     double sum = 0, worst = 0;
     int samples = 0;
@@ -95,9 +106,17 @@ int main(int argc, char **argv) {
             double best = 1e30;
             for (int r = 0; r < reps; r++) {
                 const double t0 = now_ms();
-                if (renderer->render_volume(reinterpret_cast<uchar4 *>(frame.data()), rc) != 0) { fprintf(stderr, "render_volume failed\n"); return 1; }
+                if (renderer->render_volume(target, rc) != 0) { fprintf(stderr, "render_volume failed\n"); return 1; }
                 const double t = now_ms() - t0;
                 if (t < best) best = t;
+            }
+            if (device_buffer && cudaMemcpy(frame.data(), dev_frame, frame.size() * 4, cudaMemcpyDeviceToHost) != cudaSuccess) { fprintf(stderr, "cudaMemcpy failed\n"); return 1; }
+            if (dump) {
+                char name[512];
+                snprintf(name, sizeof(name), "%s_%s_%d.rgba", dump, persp ? "persp" : "ortho", p);
+                FILE *f = fopen(name, "wb");
+                if (!f || fwrite(frame.data(), 4, frame.size(), f) != frame.size()) { fprintf(stderr, "cannot write %s\n", name); return 1; }
+                fclose(f);
             }
             size_t lit = 0;
             for (uint32_t px : frame) lit += px != 0;
@@ -115,7 +134,9 @@ int main(int argc, char **argv) {
                 }
             }
         }
-    printf("avg %.3f ms, max %.3f ms over %d frames (host buffer, blocking, D2H included)\n", sum / samples, worst, samples);
+    printf("avg %.3f ms, max %.3f ms over %d frames (%s)\n", sum / samples, worst, samples,
+           device_buffer ? "device buffer, blocking" : "host buffer, blocking, D2H included");
     delete renderer;
+    cudaFree(dev_frame);
     return 0;
 }

@@ -89,6 +89,8 @@ def lib() -> C.CDLL:
         "vr5_render": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),
         "vr5_render_raycaster": (C.c_int, [vp, vp, vp, C.c_int]),
         "vr5_render_async": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),
+        "vr5_render_sequence": (C.c_int, [vp, C.POINTER(Params), C.c_int, C.POINTER(vp)]),
+        "vr5_set_option": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
         "vr5_sync": (C.c_int, [vp]),
         "vr5_set_stream": (C.c_int, [vp, vp]),
         "vr5_set_overlap": (C.c_int, [vp, C.c_int]),
@@ -115,6 +117,8 @@ def lib() -> C.CDLL:
         "vr5_peer_release": (C.c_int, [vp, C.c_uint64]),
         "vr5_peer_read": (C.c_int, [vp, C.c_uint64, vp]),
         "vr5_peer_sync_frame": (C.c_int, [vp, C.c_uint64]),
+        "vr5_peer_render_sequence": (C.c_int, [vp, C.POINTER(Params), C.c_int, C.c_uint64]),
+        "vr5_peer_consume_sequence": (C.c_int, [vp, C.c_uint64, C.c_int, vp]),
         "vr5_peer_status": (C.c_int, [vp]),
         "vr5_peer_close": (None, [vp]),
         "vr5_hostring_bytes": (C.c_uint64, [C.c_uint16, C.c_uint16, C.c_int]),

@@ -46,7 +46,27 @@ struct Counters {
     unsigned long long rays_hit, rays_accum, esl_iters, samples, shaded;
 };
 
+// One frame of a frame SEQUENCE (vr5_render_sequence / vr5_peer_render_sequence): what changes from frame to frame. The
+// persistent grid pulls the tiles of all frames of the sequence from ONE queue (frame = slot / n_queue), so a launch has one
+// tail however many frames it renders, and the host submits a whole camera path with one call. 80 bytes, 16-byte aligned.
+struct FrameView {
+    float ox, oy, oz, dx, dy, dz, rx, ry, rz, ux, uy, uz;  // origin, direction, right_plane, up_plane of the frame's View
+    uchar4 *out;               // the frame's buffer (a slot of a frame ring, possibly in a peer GPU's memory)
+    // frame-ring hand-shake (vr5_peer.cu), both optional:
+    uint32_t *arrive;          // += 1 (system scope, behind a system fence) by the warp that finishes this rank's last tile of the frame
+    const uint32_t *consumed;  // must reach `consumed_target` (acquire, system scope) before any pixel of the frame is stored
+    uint32_t consumed_target, pad;
+};
+static_assert(sizeof(FrameView) == 80, "FrameView layout");
+
+struct RayView { float ox, oy, oz, dx, dy, dz, rx, ry, rz, ux, uy, uz; };
+
 struct KArgs {
+    // frame sequence: NULL / 1 for a single frame, whose view and buffer are the fields below
+    const FrameView *frames;
+    uint32_t n_frames;
+    uint32_t *frame_done;    // sequence with hand-shake: queue slots finished per frame (zeroed before the launch)
+    uint32_t *timed_out;     // set when a wait for `consumed` gives up (bounded: a missing consumer must not hang the GPU)
     // view (ViewBase.h:14-21)
     float ox, oy, oz;        // origin
     float dx, dy, dz;        // direction
@@ -98,6 +118,9 @@ struct KArgs {
     const uint32_t *group_order;  // permutation of the groups (build_group_order) or NULL: row-major
     int cta_fetch;           // 1: a CTA takes 8 queue slots at a time (one barrier per block), 0: every warp takes its own
     Counters *counters;
+    // host side only: largest per-step displacement of a ray in voxels over the frame(s) (+inf when a view is not finite or
+    // degenerate); the launcher compares it with the guard margins of the unclamped variants (vr5_render.cu, reach_ok)
+    float reach;
 };
 
 // ---- exact fp32 helpers ----------------------------------------------------------------------------------
@@ -220,22 +243,22 @@ template <int V> struct FetchTag { static constexpr int value = V; };
 
 // ---- one ray (CPURenderer.cpp:11-41). Returns the packed RGBA8 pixel; 0 when the reference leaves it cleared. ----
 template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
-__device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const VolScale &vs, const Window &win, uint32_t lut_addr, const uint32_t *esl_bits,
+__device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, const VolScale &vs, const Window &win, uint32_t lut_addr, const uint32_t *esl_bits,
                                              float step, float threshold, int col, int row, Counters &cnt) {
     // View::get_ray (ViewBase.h:23-35)
     const float cx = (float)(col - a.half_w);
     const float cy = (float)(row - a.half_h);
     float ox, oy, oz, dx, dy, dz;
     if (a.perspective) {
-        ox = a.ox; oy = a.oy; oz = a.oz;
-        dx = fadd(fadd(a.dx, fmul(a.rx, cx)), fmul(a.ux, cy));
-        dy = fadd(fadd(a.dy, fmul(a.ry, cx)), fmul(a.uy, cy));
-        dz = fadd(fadd(a.dz, fmul(a.rz, cx)), fmul(a.uz, cy));
+        ox = v.ox; oy = v.oy; oz = v.oz;
+        dx = fadd(fadd(v.dx, fmul(v.rx, cx)), fmul(v.ux, cy));
+        dy = fadd(fadd(v.dy, fmul(v.ry, cx)), fmul(v.uy, cy));
+        dz = fadd(fadd(v.dz, fmul(v.rz, cx)), fmul(v.uz, cy));
     } else {
-        dx = a.dx; dy = a.dy; dz = a.dz;
-        ox = fadd(fadd(a.ox, fmul(a.rx, cx)), fmul(a.ux, cy));
-        oy = fadd(fadd(a.oy, fmul(a.ry, cx)), fmul(a.uy, cy));
-        oz = fadd(fadd(a.oz, fmul(a.rz, cx)), fmul(a.uz, cy));
+        dx = v.dx; dy = v.dy; dz = v.dz;
+        ox = fadd(fadd(v.ox, fmul(v.rx, cx)), fmul(v.ux, cy));
+        oy = fadd(fadd(v.oy, fmul(v.ry, cx)), fmul(v.uy, cy));
+        oz = fadd(fadd(v.oz, fmul(v.rz, cx)), fmul(v.uz, cy));
     }
     // Raycaster::intersect (RaycasterBase.h:32-42); the zero fix-up applies to a local copy only
     float k, k_far;
@@ -457,7 +480,118 @@ __device__ __forceinline__ void tile_of_slot(const KArgs &a, uint32_t q, uint32_
     tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
 }
 
-// ---- the kernel: persistent warps + atomic tile queue -----------------------------------------------------------------
+// ---- persistent warps + atomic tile queue (shared by cast_kernel and tri_kernel) -------------------------------------------
+__device__ __forceinline__ uint32_t load_acquire_sys_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// view of frame f: kernel parameters for a single frame, the device array for a sequence (uniform loads, once per tile;
+// nothing of it stays live across the march)
+__device__ __forceinline__ RayView load_view(const KArgs &a, uint32_t f) {
+    if (a.frames) {
+        const float4 *p = reinterpret_cast<const float4 *>(a.frames + f);
+        const float4 x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
+        return RayView{x.x, x.y, x.z, x.w, y.x, y.y, y.z, y.w, z.x, z.y, z.z, z.w};
+    }
+    return RayView{a.ox, a.oy, a.oz, a.dx, a.dy, a.dz, a.rx, a.ry, a.rz, a.ux, a.uy, a.uz};
+}
+
+// `count` queue slots of frame f are finished (their pixels stored and fenced): the warp that completes the frame's last slot
+// publishes the rank's arrival in the frame ring. Called by one thread.
+__device__ __forceinline__ void frame_slots_done(const KArgs &a, uint32_t f, uint32_t count) {
+    if (atomicAdd(a.frame_done + f, count) + count == a.n_queue) {
+        const FrameView &fv = a.frames[f];
+        if (fv.arrive) {
+            __threadfence_system();
+            atomicAdd_system(fv.arrive, 1u);
+        }
+    }
+}
+
+// The slot of frame f may be written once the consumer has released the frame that used it before. Frames are released in
+// order, so one shared "highest frame known to be writable" per CTA saves all but the first poll of a frame. Bounded: after
+// 4 s the wait gives up, raises the status flag and the frame is written anyway (a lost consumer must not hang the device).
+__device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, volatile uint32_t *s_ok) {
+    if (*s_ok != 0xffffffffu && *s_ok >= f) return;
+    const FrameView &fv = a.frames[f];
+    if (fv.consumed) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int32_t)(load_acquire_sys_u32(fv.consumed) - fv.consumed_target) < 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > 4000000000ull) { *a.timed_out = 1u; break; }
+            __nanosleep(200);
+        }
+    }
+    *s_ok = f;
+}
+
+// ray(view, col, row) -> RGBA8 pixel. COUNT: instrumented pass, nothing is stored.
+template <bool COUNT, class RayFn>
+__device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
+    const int lane = threadIdx.x & 31;
+    __shared__ unsigned s_q;
+    __shared__ uint32_t s_ok;   // sequence hand-shake: highest frame whose slot is known to be writable (0xffffffff: none yet)
+    const bool shake = a.frames && a.frame_done;
+    if (shake) {
+        if (threadIdx.x == 0) s_ok = 0xffffffffu;
+        __syncthreads();
+    }
+    const uint32_t n_total = a.n_queue * a.n_frames;
+    uint32_t f_prev = 0xffffffffu;   // CTA fetch: frame of the block this CTA has just finished
+    for (;;) {
+        unsigned q = 0;
+        if (a.cta_fetch) {
+            // the CTA takes 8 consecutive queue slots at once = a 32x8-pixel block (queue groups are 4 tiles wide): its 8
+            // warps march through neighbouring voxels in step and share L1 lines (C3: 0.606 -> 0.596 ms). The price is a
+            // barrier per block, so the host only asks for it when rays of neighbouring tiles end together (no opaque TF
+            // entry: C4 measured 5 % slower with it). Same counter arithmetic as one slot per warp.
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                if (shake && f_prev != 0xffffffffu) frame_slots_done(a, f_prev, (uint32_t)(kCtaThreads / 32));
+                s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
+            }
+            __syncthreads();
+            q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
+        } else {
+            if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
+            q = __shfl_sync(0xffffffffu, q, 0);
+        }
+        if (q >= n_total) break;
+        uint32_t f = 0, qi = q;
+        if (a.frames) { f = q / a.n_queue; qi = q - f * a.n_queue; }   // a block of 8 never straddles frames (n_queue % 32 == 0)
+        f_prev = f;
+        if (shake && !COUNT) {   // before the march: the frame's slot is almost always free long since
+            if (lane == 0) wait_frame_writable(a, f, &s_ok);
+            __syncwarp();
+        }
+        uint32_t tx, tyl;
+        tile_of_slot(a, qi, tx, tyl);
+        const int col = (int)tx * kTileW + (lane & 7);
+        const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
+        if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle
+            const RayView v = load_view(a, f);
+            const uint32_t rgba = ray(v, col, row);
+            if (!COUNT) {
+                uchar4 *out = a.frames ? a.frames[f].out : a.out;
+                const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
+                reinterpret_cast<uint32_t *>(out)[(size_t)out_row * a.width + col] = rgba;
+            }
+        }
+        if (shake) {
+            __threadfence_system();   // this lane's pixels are visible system-wide before the slot is counted
+            if (!a.cta_fetch) {
+                __syncwarp();
+                if (lane == 0) frame_slots_done(a, f, 1u);
+            }
+        }
+    }
+}
+
+// ---- the kernel ---------------------------------------------------------------------------------------------------------
 // SHADE=false is chosen by the host when no sample can take the shading path (light_kd <= 0.01 or no TF entry with
 // alpha > 0.05), CLAMP=false when the sampler is the padded 3-D texture and min_bound == (-1,-1,-1).
 template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
@@ -478,35 +612,9 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
     if (SAMPLER >= 4) win = Window{pinned->wmx, pinned->wmy, pinned->wmz, pinned->whi, pinned->wsx, pinned->wsxy};
     const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_lut);
     Counters cnt = {0, 0, 0, 0, 0};
-    __shared__ unsigned s_q;
-    for (;;) {
-        unsigned q = 0;
-        if (a.cta_fetch) {
-            // the CTA takes 8 consecutive queue slots at once = a 32x8-pixel block (queue groups are 4 tiles wide): its 8
-            // warps march through neighbouring voxels in step and share L1 lines (C3: 0.606 -> 0.596 ms). The price is a
-            // barrier per block, so the host only asks for it when rays of neighbouring tiles end together (no opaque TF
-            // entry: C4 measured 5 % slower with it). Same counter arithmetic as one slot per warp.
-            __syncthreads();
-            if (threadIdx.x == 0) s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
-            __syncthreads();
-            q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
-        } else {
-            if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
-            q = __shfl_sync(0xffffffffu, q, 0);
-        }
-        if (q >= a.n_queue) break;
-        uint32_t tx, tyl;
-        tile_of_slot(a, q, tx, tyl);
-        const int col = (int)tx * kTileW + (lane & 7);
-        const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
-        if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle
-            const uint32_t rgba = cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, vs, win, lut_addr, s_esl, step, threshold, col, row, cnt);
-            if (!COUNT) {
-                const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
-                reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;
-            }
-        }
-    }
+    run_tile_queue<COUNT>(a, [&](const RayView &v, int col, int row) {
+        return cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, v, vs, win, lut_addr, s_esl, step, threshold, col, row, cnt);
+    });
     if (COUNT) {
         unsigned long long v[5] = {cnt.rays_hit, cnt.rays_accum, cnt.esl_iters, cnt.samples, cnt.shaded};
         unsigned long long *dst = reinterpret_cast<unsigned long long *>(a.counters);

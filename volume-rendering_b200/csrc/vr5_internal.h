@@ -78,6 +78,24 @@ struct vr5_renderer {
     // tile-queue group order (vr5_render.cu, build_group_order): device table and the geometry it was built for
     uint32_t *d_group_order = nullptr;
     uint32_t order_key[6] = {0, 0, 0, 0, 0, 0};  // width, height, rank, world, packed, mode
+    // frame sequences (vr5_render_sequence, vr5_peer_render_sequence): ONE persistent launch renders all frames of a camera
+    // path from one tile queue; own monotonic queue counter (the launches run on `stream`, in order)
+    unsigned *d_seq_queue = nullptr;
+    uint32_t seq_queue_base = 0;
+    // consumer side of a frame ring driven by sequences (vr5_peer_consume_sequence): stream memory operations on their own stream
+    cudaStream_t consumer_stream = nullptr;
+    cudaEvent_t consumer_done = nullptr;
+    bool consumer_pending = false;
+    // experiment knobs: read from the environment ONCE in vr5_create, changed afterwards only through vr5_set_option
+    struct Options {
+        int queue_order = 0;        // VR5_QUEUE_ORDER: 0 rows (default), 1 cols, 2 rings
+        bool warp_fetch = false;    // VR5_WARP_FETCH: every warp takes its own queue slot even when the TF has no opaque entry
+        bool tri_clamped = false;   // VR5_TRI_CLAMPED: trilinear march with clamped record indices
+        int trif_ctas = 6;          // VR5_TRIF_CTAS: register budget of the contracted trilinear march (CTAs per SM)
+        int trif_depth = 2;         // VR5_TRIF_DEPTH: cell requests in flight per ray
+        bool no_p2 = false;         // VR5_NO_P2: never build the power-of-two window
+        uint32_t win_sx = 0;        // VR5_WIN_SX: row stride of the window layouts (0 = default)
+    } opt;
     // bookkeeping
     int ctas_per_sm[512] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
@@ -93,6 +111,15 @@ int vr5_lane_begin(vr5_renderer *r, int lane);
 int vr5_lane_end(vr5_renderer *r, int lane);
 int vr5_render_into(vr5_renderer *r, const struct vr5_params *p, void *out_dev, int lane);  // async launch of the cast kernel, device buffer
 int vr5_adopt_volume(vr5_renderer *r, uint8_t *dev_owned, uint64_t bytes, uint16_t dx, uint16_t dy, uint16_t dz);
+// where a frame of a sequence goes and how its completion is signalled (frame-ring hand-shake words, vr5_peer.cu), both optional
+struct vr5_frame_target {
+    void *out_dev;
+    uint32_t *arrive;          // +1 (system-scope atomic, after a system fence) when this rank's last tile of the frame is stored
+    const uint32_t *consumed;  // must reach consumed_target before the frame's pixels are stored
+    uint32_t consumed_target;
+};
+// async launch of ONE persistent kernel over frames[0..n) on the renderer's stream (vr5_render.cu)
+int vr5_sequence_launch(vr5_renderer *r, const struct vr5_params *frames, int n, const vr5_frame_target *targets, uint32_t *timed_out_dev);
 
 #define VR5_CUDA(r, call)                                         \
     do {                                                          \

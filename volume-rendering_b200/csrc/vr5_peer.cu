@@ -1,10 +1,13 @@
 // vr5_peer.cu - fused render + gather over NVLink peer memory (include/vr5.h, "fused render + gather").
 // The reference is single-GPU (VolR.cpp:141-172); this replaces the render -> NCCL gather -> unpack sequence of the
 // multi-GPU bench with direct stores of every pixel into the gathering rank's frame, plus two flag words per frame.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
+#include <vector>
 
 #include "../../include/vr5.h"
 #include "vr5_internal.h"
@@ -15,8 +18,9 @@ constexpr size_t kHeaderBytes = 8192;          // flag words, one 128-byte line 
 constexpr int kMaxSlots = 16;
 constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;  // a wait that lasts 4 s gives up and raises the status flag
 
-// header layout (uint32 words, one 128-byte line per flag): [32] timed_out, [64 + 64 * slot] arrive[slot] = writer ranks that
-// finished a frame in that slot (all uses), [96 + 64 * slot] consumed[slot] = uses of that slot the owner has released.
+// header layout (uint32 words, one 128-byte line per flag): [32] timed_out, [64 + 64 * slot] arrive[slot] = ranks that
+// finished their strips of a frame in that slot (all uses; EVERY rank arrives, the owner included: a use adds `world`),
+// [96 + 64 * slot] consumed[slot] = uses of that slot the owner has released.
 // Per-slot counters keep the protocol independent of the order in which frames on different lanes complete.
 __host__ __device__ inline uint32_t *timeout_word(uint8_t *base) { return reinterpret_cast<uint32_t *>(base) + 32; }
 __host__ __device__ inline uint32_t *arrive_word(uint8_t *base, int slot) { return reinterpret_cast<uint32_t *>(base) + 64 + 64 * slot; }
@@ -41,6 +45,31 @@ __global__ void peer_wait_kernel(const uint32_t *flag, uint32_t target, uint32_t
         if (global_ns() - t0 > kWaitTimeoutNs) { *timed_out = 1u; break; }
         __nanosleep(100);
     }
+}
+
+// Stream memory operations (executed by the stream's front end, no SM slot needed - the SMs are full of persistent cast CTAs):
+// the consumer side of a ring driven by frame sequences waits for arrive[slot] and stores consumed[slot] with them. Resolved
+// at run time; one-thread kernels are the fallback.
+typedef CUresult (*WaitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+typedef CUresult (*WriteValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+struct MemOps { WaitValue32 wait = nullptr; WriteValue32 write = nullptr; };
+const MemOps &mem_ops() {
+    static MemOps ops;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        cudaDriverEntryPointQueryResult q;
+        void *w = nullptr, *x = nullptr;
+        if (!getenv("VR5_PEER_FLAG_KERNELS") &&
+            cudaGetDriverEntryPoint("cuStreamWaitValue32", &w, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess &&
+            cudaGetDriverEntryPoint("cuStreamWriteValue32", &x, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) {
+            ops.wait = reinterpret_cast<WaitValue32>(w);
+            ops.write = reinterpret_cast<WriteValue32>(x);
+        } else {
+            cudaGetLastError();
+        }
+    }
+    return ops;
 }
 
 // one thread, after the cast kernel on the same stream: publish this rank's pixels, then count the arrival
@@ -148,10 +177,9 @@ extern "C" int vr5_peer_render(vr5_renderer *r, const vr5_params *p, uint64_t se
         r->launches++;
     }
     if (vr5_render_into(r, p, slot_ptr(r, seq), lane)) return 1;
-    if (!r->peer_owner) {
-        peer_arrive_kernel<<<1, 1, 0, st>>>(arrive_word(r->peer_base, slot));
-        r->launches++;
-    }
+    // every rank arrives, the owner included (its own wait is then one counter compare whichever API filled the slot)
+    peer_arrive_kernel<<<1, 1, 0, st>>>(arrive_word(r->peer_base, slot));
+    r->launches++;
     VR5_CUDA(r, cudaGetLastError());
     return vr5_lane_end(r, lane);
 }
@@ -161,9 +189,9 @@ extern "C" int vr5_peer_wait(vr5_renderer *r, uint64_t seq, void **frame_dev_out
     if (!r->peer_owner) { vr5_fail(r, "vr5_peer_wait: only the owner waits for frames", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     const uint64_t slots = (uint64_t)r->peer_slots;
-    if (r->world > 1) {
-        // every use of a slot adds world - 1 arrivals to its counter
-        const uint32_t target = (uint32_t)((seq / slots + 1) * (uint64_t)(r->world - 1));
+    {
+        // every use of a slot adds `world` arrivals to its counter
+        const uint32_t target = (uint32_t)((seq / slots + 1) * (uint64_t)r->world);
         peer_wait_kernel<<<1, 1, 0, vr5_lane_stream(r, lane_of(r, seq))>>>(arrive_word(r->peer_base, (int)(seq % slots)), target, timeout_word(r->peer_base));
         r->launches++;
         VR5_CUDA(r, cudaGetLastError());
@@ -210,5 +238,63 @@ extern "C" int vr5_peer_status(vr5_renderer *r) {
     VR5_CUDA(r, cudaMemcpyAsync(&flag, timeout_word(r->peer_base), sizeof(flag), cudaMemcpyDeviceToHost, r->stream));
     VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     if (flag) { vr5_fail(r, "peer ring: a device-side wait timed out (a rank is missing or out of frame order)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    return 0;
+}
+
+// ---- frame sequences through the ring ---------------------------------------------------------------------------------------
+// ONE persistent launch per rank renders frames seq0 .. seq0 + n - 1 (vr5_sequence_launch): the hand-shake moves into the
+// kernel. Before a warp stores pixels of a frame it makes sure the frame that used the slot before has been released
+// (consumed[slot], acquire load, cached per CTA); the warp that finishes a rank's last tile of a frame adds the rank's arrival
+// (system fence + system-scope atomic on arrive[slot]). No wait / arrive kernels, no per-frame launches, one call per camera path.
+extern "C" int vr5_peer_render_sequence(vr5_renderer *r, const vr5_params *frames, int n, uint64_t seq0) {
+    if (!r) return 1;
+    if (!r->peer_base) { vr5_fail(r, "vr5_peer_render_sequence: no ring (vr5_peer_create / vr5_peer_open)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (r->packed) { vr5_fail(r, "vr5_peer_render_sequence: the partition must be unpacked (pixels go to their final place)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (!frames || n < 1) { vr5_fail(r, "vr5_peer_render_sequence: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    const uint64_t slots = (uint64_t)r->peer_slots;
+    std::vector<vr5_frame_target> t((size_t)n);
+    for (int i = 0; i < n; i++) {
+        const uint64_t seq = seq0 + (uint64_t)i;
+        const int slot = (int)(seq % slots);
+        const uint32_t use = (uint32_t)(seq / slots);
+        t[(size_t)i] = vr5_frame_target{slot_ptr(r, seq), arrive_word(r->peer_base, slot), use ? consumed_word(r->peer_base, slot) : nullptr, use};
+    }
+    return vr5_sequence_launch(r, frames, n, t.data(), timeout_word(r->peer_base));
+}
+
+// owner: consume frames seq0 .. seq0 + n - 1 in order, on the renderer's consumer stream (asynchronous; vr5_join / vr5_sync
+// wait for it): wait for all `world` arrivals of a frame, optionally copy it (device to device) to copy_dst_dev + i *
+// width * height * 4 - what a consumer does with a frame - and release its slot.
+extern "C" int vr5_peer_consume_sequence(vr5_renderer *r, uint64_t seq0, int n, void *copy_dst_dev) {
+    if (!r) return 1;
+    if (!r->peer_owner) { vr5_fail(r, "vr5_peer_consume_sequence: only the owner consumes frames", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (n < 1) { vr5_fail(r, "vr5_peer_consume_sequence: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    const uint64_t slots = (uint64_t)r->peer_slots;
+    const MemOps &ops = mem_ops();
+    cudaStream_t st = r->consumer_stream;
+    for (int i = 0; i < n; i++) {
+        const uint64_t seq = seq0 + (uint64_t)i;
+        const int slot = (int)(seq % slots);
+        const uint32_t use = (uint32_t)(seq / slots);
+        if (use != r->peer_released_slot[slot]) { vr5_fail(r, "vr5_peer_consume_sequence: every frame of a slot is released once, in order", cudaSuccess, __FILE__, __LINE__); return 1; }
+        const uint32_t target = (use + 1u) * (uint32_t)r->world;
+        uint32_t *arrive = arrive_word(r->peer_base, slot), *consumed = consumed_word(r->peer_base, slot);
+        if (!ops.wait || ops.wait((CUstream)st, (CUdeviceptr)(uintptr_t)arrive, target, CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS) {
+            peer_wait_kernel<<<1, 1, 0, st>>>(arrive, target, timeout_word(r->peer_base));
+            r->launches++;
+        }
+        if (copy_dst_dev)
+            VR5_CUDA(r, cudaMemcpyAsync(static_cast<uint8_t *>(copy_dst_dev) + (size_t)i * r->frame_bytes, slot_ptr(r, seq), r->frame_bytes, cudaMemcpyDeviceToDevice, st));
+        if (!ops.write || ops.write((CUstream)st, (CUdeviceptr)(uintptr_t)consumed, use + 1u, CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS) {
+            peer_release_kernel<<<1, 1, 0, st>>>(consumed, use + 1u);
+            r->launches++;
+        }
+        r->peer_released_slot[slot]++;
+    }
+    VR5_CUDA(r, cudaGetLastError());
+    VR5_CUDA(r, cudaEventRecord(r->consumer_done, st));
+    r->consumer_pending = true;
     return 0;
 }

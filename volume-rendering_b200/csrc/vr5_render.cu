@@ -133,6 +133,11 @@ static cudaError_t sync_all(vr5_renderer *r) {
         if (first == cudaSuccess) first = e;
         ln.pending = false;
     }
+    if (r->consumer_stream) {
+        const cudaError_t e = cudaStreamSynchronize(r->consumer_stream);
+        if (first == cudaSuccess) first = e;
+        r->consumer_pending = false;
+    }
     return first;
 }
 
@@ -175,6 +180,7 @@ extern "C" int vr5_join(vr5_renderer *r) {
     VR5_CUDA(r, cudaSetDevice(r->device));
     for (int i = 0; i < r->n_lanes && r->n_lanes > 1; i++)
         if (r->lanes[i].pending) { VR5_CUDA(r, cudaStreamWaitEvent(r->stream, r->lanes[i].done, 0)); r->lanes[i].pending = false; }
+    if (r->consumer_pending) { VR5_CUDA(r, cudaStreamWaitEvent(r->stream, r->consumer_done, 0)); r->consumer_pending = false; }
     return 0;
 }
 
@@ -222,6 +228,14 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     }
     if ((e = cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaMalloc(&r->d_counters, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc counters", e);
+    if ((e = cudaMalloc(&r->d_seq_queue, 128)) != cudaSuccess) return bail("cudaMalloc sequence queue", e);
+    if ((e = cudaMemset(r->d_seq_queue, 0, 128)) != cudaSuccess) return bail("cudaMemset sequence queue", e);
+    if ((e = cudaStreamCreateWithFlags(&r->consumer_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate consumer", e);
+    if ((e = cudaEventCreateWithFlags(&r->consumer_done, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    // experiment knobs: the environment is read here, once; the launch path only looks at r->opt (vr5_set_option changes it)
+    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX"})
+        if (const char *v = getenv(name)) vr5_set_option(r, name, v);
+    r->err.clear();
     const char *env = getenv("VR5_SAMPLER");
     r->sampler = VR5_SAMPLER_HYBRID_WINDOW;  // fastest path on B200 (profiles/r01_sampler_choice.md); $VR5_SAMPLER overrides
     if (env) {
@@ -309,6 +323,9 @@ extern "C" void vr5_destroy(vr5_renderer *r) {
         if (ln.stream) cudaStreamDestroy(ln.stream);
     }
     if (r->ev_fork) cudaEventDestroy(r->ev_fork);
+    if (r->consumer_done) cudaEventDestroy(r->consumer_done);
+    if (r->consumer_stream) cudaStreamDestroy(r->consumer_stream);
+    cudaFree(r->d_seq_queue);
     cudaFree(r->d_tf);
     cudaFree(r->d_esl);
     cudaFree(r->d_counters);
@@ -322,6 +339,11 @@ extern "C" int vr5_set_window(vr5_renderer *r, uint16_t width, uint16_t height) 
     if (!r) return 1;
     VR5_CUDA(r, cudaSetDevice(r->device));
     if (width == 0 || height == 0) { vr5_fail(r, "vr5_set_window: empty viewport", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if ((r->peer_base || r->hr_base) && (width != r->width || height != r->height)) {
+        // a ring's slots are sized for the window it was created with: a larger window would write past them
+        vr5_fail(r, "vr5_set_window: a frame ring is attached (vr5_peer_close / vr5_hostring_detach first)", cudaSuccess, __FILE__, __LINE__);
+        return 1;
+    }
     VR5_CUDA(r, sync_all(r));
     for (auto &ln : r->lanes) if (ln.d_frame) { cudaFree(ln.d_frame); ln.d_frame = nullptr; }
     r->width = width; r->height = height;
@@ -360,7 +382,7 @@ static int build_padded(vr5_renderer *r) {
 // cannot live inside one 4-GiB address window; the launcher then falls back to the texture path.
 static int build_window(vr5_renderer *r) {
     uint64_t sx = r->nx + 2 < 32 ? 32 : r->nx + 2, sy = r->ny + 2 < 32 ? 32 : r->ny + 2;  // sxy >= 1024 keeps wmz below 2^23
-    if (const char *e = getenv("VR5_WIN_SX")) { const uint64_t v = strtoull(e, nullptr, 10); if (v >= sx && v <= 65536) sx = v; }  // experiment knob
+    if (r->opt.win_sx >= sx && r->opt.win_sx <= 65536) sx = r->opt.win_sx;  // experiment knob
     const uint64_t sxy = sx * sy, core = sxy * (r->nz + 2);
     const uint64_t margin = ((uint64_t)kWindowGuard * (sxy + sx + 1) + 255) & ~255ull;
     const uint64_t total = core + 2 * margin;
@@ -417,7 +439,7 @@ static int build_p2(vr5_renderer *r) {
     const uint32_t G = kP2Origin;
     // strides are deliberately NOT powers of two: 1024-byte rows measured 10 % slower than 514-byte ones (cache-set aliasing)
     uint32_t sx = r->nx + 2 * G + 2;
-    if (const char *e = getenv("VR5_WIN_SX")) { const uint32_t v = (uint32_t)strtoul(e, nullptr, 10); if (v >= r->nx + 2 * G && v <= 65536) sx = v; }  // experiment knob
+    if (r->opt.win_sx >= r->nx + 2 * G && r->opt.win_sx <= 65536) sx = r->opt.win_sx;  // experiment knob
     const uint32_t rows = r->ny + 2 * G;
     const uint32_t sz = r->nz + 2 * G;
     const uint64_t size = (uint64_t)sz * rows * sx;
@@ -519,7 +541,7 @@ static int build_layout(vr5_renderer *r) {
         return 0;
     }
     if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW) {
-        if (!getenv("VR5_NO_P2") && build_p2(r)) return 1;
+        if (!r->opt.no_p2 && build_p2(r)) return 1;
         if (!r->p2_wl && build_window(r)) return 1;
         VR5_CUDA(r, cudaStreamSynchronize(r->stream));
     }
@@ -664,7 +686,7 @@ static cudaError_t launch_one(vr5_renderer *r, const KArgs &a) {
         if (per_sm < 1) per_sm = 1;
     }
     uint32_t grid = (uint32_t)(r->num_sms * per_sm);  // persistent: every CTA resident, a multiple of the SM count
-    const uint32_t needed = (a.n_queue + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
+    const uint32_t needed = (a.n_queue * a.n_frames + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
     if (grid > needed) grid = needed ? needed : 1;
     cast_kernel<S, C, SH, CL><<<grid, kCtaThreads, 0, r->launch_stream>>>(a);
     r->last_grid = grid;
@@ -687,12 +709,23 @@ static cudaError_t launch_sc(vr5_renderer *r, const KArgs &a, bool count, bool s
 // inside out. Both cut the tail of a LONE launch (trilinear-fma: 1.275 -> 1.224 ms with rings) and both lose in the overlapped
 // stream of frames, where the next frame fills the tail anyway and their wider working set costs L1/L2 hits (nearest: 0.561 ->
 // 0.577 / 0.582 ms per frame). Default therefore: row-major, no table; VR5_QUEUE_ORDER=cols|rings selects the others.
-static int queue_order_mode(const KArgs *a) {
-    const char *e = getenv("VR5_QUEUE_ORDER");
-    if (getenv("VR5_ROW_MAJOR") || (e && !strcmp(e, "rows"))) return 0;
-    if (e && !strcmp(e, "rings")) return 2;
-    if (e && !strcmp(e, "cols")) return 1;
-    (void)a;
+// Experiment knobs (names = the environment variables vr5_create reads once). Returns 1 for an unknown name or a bad value.
+extern "C" int vr5_set_option(vr5_renderer *r, const char *name, const char *value) {
+    if (!r || !name || !value) return 1;
+    auto truthy = [&]() { return value[0] != '\0' && strcmp(value, "0") != 0; };
+    if (!strcmp(name, "VR5_QUEUE_ORDER")) {
+        if (!strcmp(value, "rows")) r->opt.queue_order = 0;
+        else if (!strcmp(value, "cols")) r->opt.queue_order = 1;
+        else if (!strcmp(value, "rings")) r->opt.queue_order = 2;
+        else { vr5_fail(r, "vr5_set_option: VR5_QUEUE_ORDER is rows, cols or rings", cudaSuccess, __FILE__, __LINE__); return 1; }
+    } else if (!strcmp(name, "VR5_ROW_MAJOR")) { if (truthy()) r->opt.queue_order = 0; }
+    else if (!strcmp(name, "VR5_WARP_FETCH")) r->opt.warp_fetch = truthy();
+    else if (!strcmp(name, "VR5_TRI_CLAMPED")) r->opt.tri_clamped = truthy();
+    else if (!strcmp(name, "VR5_TRIF_CTAS")) r->opt.trif_ctas = atoi(value);
+    else if (!strcmp(name, "VR5_TRIF_DEPTH")) r->opt.trif_depth = atoi(value);
+    else if (!strcmp(name, "VR5_NO_P2")) r->opt.no_p2 = truthy();        // takes effect at the next layout build
+    else if (!strcmp(name, "VR5_WIN_SX")) r->opt.win_sx = (uint32_t)strtoul(value, nullptr, 10);
+    else { vr5_fail(r, "vr5_set_option: unknown option", cudaSuccess, __FILE__, __LINE__); return 1; }
     return 0;
 }
 
@@ -728,6 +761,49 @@ static int build_group_order(vr5_renderer *r, const KArgs *a, int mode) {
     return 0;
 }
 
+// Largest displacement of a march step in voxels, on any axis, over all rays of a frame (d is affine in the pixel position,
+// so the four image corners bound it). The unclamped kernel variants fetch up to a few steps past a ray's clip interval and
+// rely on the guard margins of their layouts covering that reach: the launcher compares this figure with the margin
+// (reach_ok). +inf - which sends the frame through the clamped variants - for anything that is not finite and for DEGENERATE
+// views: Raycaster::intersect replaces an exactly-zero direction component by 1e-5 on a local copy only (RaycasterBase.h:
+// 33-35), so a ray whose origin lies outside [-1, 1] on that axis can receive a valid interval at k ~ 1e5 x distance while
+// its points stay outside the cube on that axis - possible only when every other component is tiny too (far_j <= (1 +
+// |o_j|) / |d_j| must reach such a k). The reference's cameras never produce that (|d| ~ 1), but the ABI accepts any View
+// bytes, so frames in which |d|_inf could fall below the bound derived here take the clamped path.
+static float frame_reach(const KArgs &a) {
+    const float inf = std::numeric_limits<float>::infinity();
+    if (!(a.step > 0.0f) || !std::isfinite(a.step)) return inf;
+    const float o[12] = {a.ox, a.oy, a.oz, a.rx, a.ry, a.rz, a.ux, a.uy, a.uz, a.dx, a.dy, a.dz};
+    for (float v : o) if (!std::isfinite(v)) return inf;
+    float reach = 0.0f, omax = 0.0f;
+    for (int c = 0; c < 4; c++) {
+        const float cx = (c & 1) ? (float)(a.width - 1 - a.half_w) : (float)(-a.half_w);
+        const float cy = (c & 2) ? (float)(a.height - 1 - a.half_h) : (float)(-a.half_h);
+        float dx = a.dx, dy = a.dy, dz = a.dz, ox = a.ox, oy = a.oy, oz = a.oz;
+        if (a.perspective) { dx += a.rx * cx + a.ux * cy; dy += a.ry * cx + a.uy * cy; dz += a.rz * cx + a.uz * cy; }
+        else { ox += a.rx * cx + a.ux * cy; oy += a.ry * cx + a.uy * cy; oz += a.rz * cx + a.uz * cy; }
+        reach = fmaxf(reach, fmaxf(fabsf(dx) * a.step * a.hx, fmaxf(fabsf(dy) * a.step * a.hy, fabsf(dz) * a.step * a.hz)));
+        omax = fmaxf(omax, fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz))));
+    }
+    if (!std::isfinite(reach) || !std::isfinite(omax)) return inf;
+    // lower bound of |d|_inf over the frame: the direction itself (orthographic), or the distance of the origin from the
+    // plane { direction + right * cx + up * cy } divided by sqrt(3) (perspective)
+    float dmin;
+    if (a.perspective) {
+        const float nx = a.ry * a.uz - a.rz * a.uy, ny = a.rz * a.ux - a.rx * a.uz, nz = a.rx * a.uy - a.ry * a.ux;
+        const float nn = sqrtf(nx * nx + ny * ny + nz * nz);
+        dmin = nn > 0.0f ? fabsf(a.dx * nx + a.dy * ny + a.dz * nz) / nn * 0.57735f : 0.0f;
+    } else {
+        dmin = fmaxf(fabsf(a.dx), fmaxf(fabsf(a.dy), fabsf(a.dz)));
+    }
+    // a degenerate hit needs k >= (|o_axis| - 1) / 1e-5 with the point more than (guard - 2) voxels outside the grid, i.e.
+    // |o_axis| - 1 > 2 (guard - 2) / n; and far_j >= k for every other axis, i.e. |d_j| <= (1 + |o_j|) * 1e-5 * n / (2 (guard - 2))
+    const float guard = (float)((kWindowGuard < kTriGuard ? kWindowGuard : kTriGuard) - 2);
+    const float bound = (1.0f + omax) * 1e-5f * fmaxf(a.hx, fmaxf(a.hy, a.hz)) / guard;
+    if (!(dmin > 2.0f * bound)) return inf;
+    return reach;
+}
+
 static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs *a) {
     if (!p) { vr5_fail(r, "vr5_render: NULL params", cudaSuccess, __FILE__, __LINE__); return 1; }
     // the reference's own guard (GPURenderer1.cu:101-102): volume, TF + ESL table, buffer
@@ -735,6 +811,7 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     if (p->view.dims.x != r->width || p->view.dims.y != r->height) { vr5_fail(r, "vr5_render: view dims differ from vr5_set_window", cudaSuccess, __FILE__, __LINE__); return 1; }
     if (p->esl && (p->esl_block_dims == 0 || p->esl_block_dims > 65535u)) { vr5_fail(r, "vr5_render: esl_block_dims must be in 1..65535", cudaSuccess, __FILE__, __LINE__); return 1; }
     memset(a, 0, sizeof(*a));
+    a->n_frames = 1;
     const vr5_view &v = p->view;
     a->ox = v.origin.x; a->oy = v.origin.y; a->oz = v.origin.z;
     a->dx = v.direction.x; a->dy = v.direction.y; a->dz = v.direction.z;
@@ -771,16 +848,17 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     a->tiles_x = (a->width + kTileW - 1) / kTileW;
     const uint32_t strips = (a->height + kTileH - 1) / kTileH;
     a->tile_rows_local = (uint32_t)r->rank < strips ? (strips - r->rank + r->world - 1) / r->world : 0;
-    a->cta_fetch = (!r->tf_opaque && !getenv("VR5_WARP_FETCH")) ? 1 : 0;
+    a->cta_fetch = (!r->tf_opaque && !r->opt.warp_fetch) ? 1 : 0;
     a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
     a->groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
     a->n_queue = (a->groups_x * a->groups_y) << (kGroupLog2X + kGroupLog2Y);
     a->group_order = nullptr;
-    if (const int mode = a->n_queue ? queue_order_mode(a) : 0) {
+    if (const int mode = a->n_queue ? r->opt.queue_order : 0) {
         if (build_group_order(r, a, mode)) return 1;
         a->group_order = r->d_group_order;
     }
     a->counters = reinterpret_cast<Counters *>(r->d_counters);
+    a->reach = frame_reach(*a);
     return 0;
 }
 
@@ -793,25 +871,7 @@ static bool window_ok(const vr5_renderer *r, const KArgs &a) {
     return reach_ok(a, (float)((r->p2_wl ? kP2Origin : kWindowGuard) - 2) / (float)kPrefetch);
 }
 
-// true when no march step of the frame moves more than `lim` voxels on any axis (callers divide their guard margin by the
-// number of steps a speculative fetch may run past the clip interval)
-static bool reach_ok(const KArgs &a, float lim) {
-    const float hx = a.hx, hy = a.hy, hz = a.hz;
-    if (!(a.step > 0.0f) || !std::isfinite(a.step)) return false;
-    for (int c = 0; c < 4; c++) {
-        float dx = a.dx, dy = a.dy, dz = a.dz;
-        if (a.perspective) {
-            const float cx = (c & 1) ? (float)(a.width - 1 - a.half_w) : (float)(-a.half_w);
-            const float cy = (c & 2) ? (float)(a.height - 1 - a.half_h) : (float)(-a.half_h);
-            dx += a.rx * cx + a.ux * cy; dy += a.ry * cx + a.uy * cy; dz += a.rz * cx + a.uz * cy;
-        }
-        const float ex = fabsf(dx) * a.step * hx, ey = fabsf(dy) * a.step * hy, ez = fabsf(dz) * a.step * hz;
-        if (!(ex <= lim) || !(ey <= lim) || !(ez <= lim)) return false;  // also rejects NaN
-    }
-    const float o[12] = {a.ox, a.oy, a.oz, a.rx, a.ry, a.rz, a.ux, a.uy, a.uz, a.dx, a.dy, a.dz};
-    for (float v : o) if (!std::isfinite(v)) return false;
-    return true;
-}
+static bool reach_ok(const KArgs &a, float lim) { return a.reach <= lim; }  // false for +inf / NaN
 
 template <int ID>
 static cudaError_t launch_p2_id(vr5_renderer *r, const KArgs &a, bool shade) {
@@ -841,12 +901,73 @@ static int launch(vr5_renderer *r, KArgs a, bool count, int lane) {
     return rc;
 }
 
+// ---- frame sequences: ONE persistent launch over all frames of a camera path ------------------------------------------------
+// The tiles of every frame go through one queue (slot / n_queue = frame), so the grid idles behind its last long rays once per
+// sequence instead of once per frame, and the host submits the whole path with one call (VolR's benchmark loop renders its
+// frames one call at a time, VolR.cpp:98-113, :225-321). Everything but the camera must be the same for all frames.
+int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const vr5_frame_target *targets, uint32_t *timed_out_dev) {
+    if (!frames || !targets || n < 1) { vr5_fail(r, "vr5_render_sequence: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
+    KArgs a;
+    if (fill_args(r, frames, targets[0].out_dev, &a)) return 1;
+    if ((uint64_t)a.n_queue * (uint64_t)n >= (1ull << 31)) { vr5_fail(r, "vr5_render_sequence: too many tiles for one queue (split the sequence)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    std::vector<FrameView> fv((size_t)n);
+    bool shake = false;
+    for (int i = 0; i < n; i++) {
+        const vr5_params &p = frames[i];
+        if (!targets[i].out_dev) { vr5_fail(r, "vr5_render_sequence: NULL frame buffer", cudaSuccess, __FILE__, __LINE__); return 1; }
+        if (i > 0) {
+            const vr5_params &q = frames[0];
+            const bool same = p.view.dims.x == q.view.dims.x && p.view.dims.y == q.view.dims.y && !p.view.perspective == !q.view.perspective &&
+                              !memcmp(&p.view.light_pos, &q.view.light_pos, sizeof(vr5_f3)) && p.ray_step == q.ray_step && p.ray_threshold == q.ray_threshold &&
+                              !p.esl == !q.esl && p.esl_block_dims == q.esl_block_dims && !memcmp(&p.esl_block_size, &q.esl_block_size, sizeof(vr5_f3)) &&
+                              p.light_kd == q.light_kd && !memcmp(&p.min_bound, &q.min_bound, sizeof(vr5_f3));
+            if (!same) { vr5_fail(r, "vr5_render_sequence: frames of a sequence may differ in origin / direction / right_plane / up_plane only", cudaSuccess, __FILE__, __LINE__); return 1; }
+            KArgs ai;   // the unclamped variants must hold for every frame: carry the largest reach
+            if (fill_args(r, &p, targets[i].out_dev, &ai)) return 1;
+            a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
+        }
+        const vr5_view &v = p.view;
+        fv[i] = FrameView{v.origin.x, v.origin.y, v.origin.z, v.direction.x, v.direction.y, v.direction.z, v.right_plane.x, v.right_plane.y, v.right_plane.z,
+                          v.up_plane.x, v.up_plane.y, v.up_plane.z, reinterpret_cast<uchar4 *>(targets[i].out_dev), targets[i].arrive, targets[i].consumed,
+                          targets[i].consumed_target, 0u};
+        shake |= targets[i].arrive || targets[i].consumed;
+    }
+    // per-sequence device block [views | done counters], allocated and freed in stream order: sequences may queue up
+    cudaStream_t st = r->stream;
+    const size_t views_bytes = (size_t)n * sizeof(FrameView), done_bytes = shake ? (size_t)n * sizeof(uint32_t) : 0;
+    uint8_t *blk = nullptr;
+    VR5_CUDA(r, cudaMallocAsync(&blk, views_bytes + done_bytes, st));
+    VR5_CUDA(r, cudaMemcpyAsync(blk, fv.data(), views_bytes, cudaMemcpyHostToDevice, st));
+    if (shake) VR5_CUDA(r, cudaMemsetAsync(blk + views_bytes, 0, done_bytes, st));
+    a.frames = reinterpret_cast<const FrameView *>(blk);
+    a.n_frames = (uint32_t)n;
+    a.frame_done = shake ? reinterpret_cast<uint32_t *>(blk + views_bytes) : nullptr;
+    a.timed_out = timed_out_dev;
+    a.queue = r->d_seq_queue;
+    a.queue_base = r->seq_queue_base;
+    r->launch_stream = st;
+    r->last_grid = 0;
+    const int rc = launch_variant(r, a, false);
+    if (r->last_grid) r->seq_queue_base += a.n_queue * (uint32_t)n + r->last_grid * (uint32_t)(kCtaThreads / 32);
+    VR5_CUDA(r, cudaFreeAsync(blk, st));
+    return rc;
+}
+
+extern "C" int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev) {
+    if (!r) return 1;
+    if (!frames || !outs_dev || n_frames < 1) { vr5_fail(r, "vr5_render_sequence: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    std::vector<vr5_frame_target> t((size_t)n_frames);
+    for (int i = 0; i < n_frames; i++) t[(size_t)i] = vr5_frame_target{outs_dev[i], nullptr, nullptr, 0u};
+    return vr5_sequence_launch(r, frames, n_frames, t.data(), nullptr);
+}
+
 static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
     // shading can only trigger when light_kd > 0.01 (folded into shade_alpha) and some TF entry has alpha > 0.05
     const bool shade = r->tf_can_shade && a.shade_alpha < std::numeric_limits<float>::infinity();
-    // the padded texture may be indexed without the upper clamp when rays are clipped to the cube it covers
     // the padded layouts may be indexed without the upper clamp when rays are clipped to the cube they cover
-    const bool cube = a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f;
+    // (a frame whose reach is not finite - degenerate or non-finite view, frame_reach - keeps every clamp)
+    const bool cube = a.mbx == -1.0f && a.mby == -1.0f && a.mbz == -1.0f && std::isfinite(a.reach);
     cudaError_t e;
     if (is_trilinear(r->sampler)) {  // GPURenderer4 semantics in software fp32 (vr5_tri.cuh); _FMA: contracted arithmetic
         TriArgs t;
@@ -862,15 +983,14 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
         t.s1 = 8u * t.cx; t.s2 = 8u * t.cx * t.cy;                       // mod 2^32 like every term of the address sum
         t.c0 = (uint32_t)base - kb * (t.s2 + t.s1 + 8u);
         // one march step may leave the cube by step * |d| * n/2 cells per axis (+1 for the cell's far corner, +1 rounding)
-        const bool fast = one_window && cube && !count && !getenv("VR5_TRI_CLAMPED") && reach_ok(a, (float)(kTriGuard - 2));
+        const bool fast = one_window && cube && !count && !r->opt.tri_clamped && reach_ok(a, (float)(kTriGuard - 2));
         // variants: instrumented (clamped, shading code present), and {clamped, unclamped} x {shading code, none}
         const bool fused = r->sampler == VR5_SAMPLER_TRILINEAR_FMA;
         int v = (count ? 0 : 1 + (fast ? 2 : 0) + (shade ? 1 : 0)) + (fused ? 5 : 0);
         int depth = 1;
         if (v == 8) {  // contracted, unclamped, no shading code: register budget x requests in flight (profiles/r01_sampler_choice.md)
-            const char *ec = getenv("VR5_TRIF_CTAS"), *ed = getenv("VR5_TRIF_DEPTH");
-            const int ctas = ec ? atoi(ec) : 6;
-            depth = ed ? atoi(ed) : 2;  // 6 CTAs per SM x 2 requests in flight measured best (profiles/r01_sampler_choice.md)
+            const int ctas = r->opt.trif_ctas;
+            depth = r->opt.trif_depth;  // default 6 CTAs per SM x 2 requests in flight measured best (profiles/r01_sampler_choice.md)
             if (depth < 1 || depth > 4) depth = 1;
             // DEPTH requests run DEPTH steps past the clip interval: all of them must stay inside the guard cells
             if (depth > 1 && !reach_ok(a, (float)(kTriGuard - 2) / (float)depth)) depth = 1;
@@ -891,7 +1011,7 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
             if (e != cudaSuccess || per_sm < 1) per_sm = 1;
         }
         uint32_t grid = (uint32_t)(r->num_sms * per_sm);
-        const uint32_t needed = (a.n_queue + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
+        const uint32_t needed = (a.n_queue * a.n_frames + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
         if (grid > needed) grid = needed ? needed : 1;
         kernels[v]<<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
         r->tri_fast = fast ? 1 : 0;

@@ -223,21 +223,21 @@ __device__ __forceinline__ void trif_classify(uint32_t pair_c, float v, float2 &
 }
 
 template <bool COUNT, bool FAST, bool SHADE, bool FMA, int DEPTH>
-__device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, int col, int row,
+__device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &rv, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, int col, int row,
                                                  Counters &cnt) {
     // View::get_ray, Raycaster::intersect and the leading empty-space loop are those of the nearest path (vr5_cast.cuh)
     const float cx = (float)(col - a.half_w), cy = (float)(row - a.half_h);
     float ox, oy, oz, dx, dy, dz;
     if (a.perspective) {
-        ox = a.ox; oy = a.oy; oz = a.oz;
-        dx = fadd(fadd(a.dx, fmul(a.rx, cx)), fmul(a.ux, cy));
-        dy = fadd(fadd(a.dy, fmul(a.ry, cx)), fmul(a.uy, cy));
-        dz = fadd(fadd(a.dz, fmul(a.rz, cx)), fmul(a.uz, cy));
+        ox = rv.ox; oy = rv.oy; oz = rv.oz;
+        dx = fadd(fadd(rv.dx, fmul(rv.rx, cx)), fmul(rv.ux, cy));
+        dy = fadd(fadd(rv.dy, fmul(rv.ry, cx)), fmul(rv.uy, cy));
+        dz = fadd(fadd(rv.dz, fmul(rv.rz, cx)), fmul(rv.uz, cy));
     } else {
-        dx = a.dx; dy = a.dy; dz = a.dz;
-        ox = fadd(fadd(a.ox, fmul(a.rx, cx)), fmul(a.ux, cy));
-        oy = fadd(fadd(a.oy, fmul(a.ry, cx)), fmul(a.uy, cy));
-        oz = fadd(fadd(a.oz, fmul(a.rz, cx)), fmul(a.uz, cy));
+        dx = rv.dx; dy = rv.dy; dz = rv.dz;
+        ox = fadd(fadd(rv.ox, fmul(rv.rx, cx)), fmul(rv.ux, cy));
+        oy = fadd(fadd(rv.oy, fmul(rv.ry, cx)), fmul(rv.uy, cy));
+        oz = fadd(fadd(rv.oz, fmul(rv.rz, cx)), fmul(rv.uz, cy));
     }
     float k, k_far;
     {
@@ -417,31 +417,9 @@ __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_con
     const TriRegs g = {a.step, a.threshold, t.hfx, t.hfy, t.hfz, t.s1, t.s2, t.c0, t.hi, pair_c, fsub(t.hfx, 0.5f), fsub(t.hfy, 0.5f), fsub(t.hfz, 0.5f)};
 #endif
     Counters cnt = {0, 0, 0, 0, 0};
-    __shared__ unsigned s_q;
-    for (;;) {
-        unsigned q = 0;
-        if (a.cta_fetch) {  // a 32x8-pixel block per CTA: its 8 warps march through neighbouring cells in step and share L1 lines (cast_kernel)
-            __syncthreads();
-            if (threadIdx.x == 0) s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
-            __syncthreads();
-            q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
-        } else {
-            if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;
-            q = __shfl_sync(0xffffffffu, q, 0);
-        }
-        if (q >= a.n_queue) break;
-        uint32_t tx, tyl;
-        tile_of_slot(a, q, tx, tyl);
-        const int col = (int)tx * kTileW + (lane & 7);
-        const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
-        if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle
-            const uint32_t rgba = cast_ray_tri<COUNT, FAST, SHADE, FMA, DEPTH>(a, t, g, s_esl, col, row, cnt);
-            if (!COUNT) {
-                const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
-                reinterpret_cast<uint32_t *>(a.out)[(size_t)out_row * a.width + col] = rgba;
-            }
-        }
-    }
+    run_tile_queue<COUNT>(a, [&](const RayView &v, int col, int row) {
+        return cast_ray_tri<COUNT, FAST, SHADE, FMA, DEPTH>(a, v, t, g, s_esl, col, row, cnt);
+    });
     if (COUNT) {
         unsigned long long v[5] = {cnt.rays_hit, cnt.rays_accum, cnt.esl_iters, cnt.samples, cnt.shaded};
         unsigned long long *dst = reinterpret_cast<unsigned long long *>(a.counters);

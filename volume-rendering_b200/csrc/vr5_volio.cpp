@@ -236,7 +236,10 @@ extern "C" int vr5_load_pvm(const char *path, uint8_t **data, uint32_t *width, u
         if (!next_line(b, pos, line) || sscanf(line.c_str(), "%g %g %g", &sx, &sy, &sz) != 3 || sx <= 0 || sy <= 0 || sz <= 0) return io_fail("vr5_load_pvm: bad voxel scale");
     }
     if (!next_line(b, pos, line) || sscanf(line.c_str(), "%u", &nc) != 1 || nc < 1) return io_fail("vr5_load_pvm: bad component count");
-    const uint64_t voxels = (uint64_t)w * h * d * nc;
+    // the four header fields are untrusted: bound them before multiplying (a product that wraps modulo 2^64 would pass the size
+    // check below with a tiny buffer); dimensions beyond 65535 cannot be rendered anyway (ushort3 dims, ModelBase.h:14)
+    if (w > 65535u || h > 65535u || d > 65535u || nc > 4u) return io_fail("vr5_load_pvm: dimensions above 65535 or more than 4 components");
+    const uint64_t voxels = (uint64_t)w * h * d * nc;   // < 2^50
     if (b.size() - pos < voxels) return io_fail("vr5_load_pvm: voxel data shorter than the header says");
     if (version < 3 && b.size() - pos != voxels) return io_fail("vr5_load_pvm: trailing bytes after the voxel data");
     *data = (uint8_t *)malloc(voxels);

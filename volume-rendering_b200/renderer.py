@@ -143,6 +143,10 @@ class GPURenderer5:
         dz, dy, dx = volume.shape
         return self._L.vr5_set_volume(self._h, _u8p(volume), volume.size, dx, dy, dz)
 
+    def set_volume_device(self, dev_ptr: int, nbytes: int, dx: int, dy: int, dz: int):
+        """Install a linear uint8 grid that already lives in device memory (device generator, NCCL broadcast)."""
+        self._check(self._L.vr5_set_volume_device(self._h, dev_ptr, nbytes, dx, dy, dz))
+
     def render_volume(self, params: Params, out: np.ndarray | None = None) -> np.ndarray:
         """Blocking render into a host array [H, W, 4] uint8 (host-pointer path of render_volume)."""
         w, h = params.view.dims[0], params.view.dims[1]
@@ -193,6 +197,16 @@ class GPURenderer5:
         ms = np.zeros(len(frames), dtype=np.float32)
         self._check(self._L.vr5_render_timed(self._h, arr, len(frames), dev_ptr, 1 if l2_flush else 0, _f32p(ms)))
         return ms
+
+    def render_sequence(self, frames, dev_ptrs):
+        """All `frames` with ONE persistent launch into the device buffers `dev_ptrs` (vr5_render_sequence); asynchronous."""
+        arr = (Params * len(frames))(*frames)
+        outs = (C.c_void_p * len(frames))(*dev_ptrs)
+        self._check(self._L.vr5_render_sequence(self._h, arr, len(frames), outs))
+
+    def set_option(self, name: str, value) -> None:
+        """Experiment knob by the name of its environment variable (vr5_set_option)."""
+        self._check(self._L.vr5_set_option(self._h, name.encode(), str(value).encode()))
 
     def sync(self):
         self._check(self._L.vr5_sync(self._h))
@@ -251,6 +265,15 @@ class GPURenderer5:
 
     def peer_release(self, seq: int):
         self._check(self._L.vr5_peer_release(self._h, seq))
+
+    def peer_render_sequence(self, frames, seq0: int):
+        """This rank's strips of frames seq0 .. seq0 + len(frames) - 1 into the ring with ONE launch; asynchronous."""
+        arr = (Params * len(frames))(*frames)
+        self._check(self._L.vr5_peer_render_sequence(self._h, arr, len(frames), seq0))
+
+    def peer_consume_sequence(self, seq0: int, n: int, copy_dst_dev: int | None = None):
+        """Owner: wait for / optionally copy out / release frames seq0 .. seq0 + n - 1 on the consumer stream."""
+        self._check(self._L.vr5_peer_consume_sequence(self._h, seq0, n, copy_dst_dev))
 
     def peer_status(self):
         self._check(self._L.vr5_peer_status(self._h))
