@@ -118,3 +118,13 @@ def test_kernel_has_no_fused_multiply_add_in_ray_math():
     assert any("tri_kernel" in f for f in with_ffma2)  # the contracted march does use the packed FMA
     mk = open(os.path.join(CSRC, "Makefile")).read()
     assert "-fmad=false" in mk and "use_fast_math" not in mk.replace("Never --use_fast_math", "")
+
+
+def test_predicted_empty_space_leap_acceptance_rule(tmp_path):
+    """vr5_cast.cuh predicts the leap count floor(dk / step) of RaycasterBase.h:67-85 with reciprocal multiplications and accepts the
+    prediction only at a stated distance from the neighbouring integers; tools/check_esl_predict.c replays the rule on the host
+    against the reference's divisions, random and adversarial (quotients within a few ulps of an integer) operands."""
+    exe = tmp_path / "check_esl"
+    subprocess.run(["gcc", "-O2", "-ffp-contract=off", os.path.join(ROOT, "tools", "check_esl_predict.c"), "-o", str(exe), "-lm"], check=True)
+    out = subprocess.run([str(exe), "5"], check=True, capture_output=True, text=True).stdout
+    assert " 0 mismatches" in out, out

@@ -14,8 +14,9 @@ the histograms), stated per class of scene:
   * decisions in play (default / opaque TF: a sample whose alpha sits near the 0.05 shading guard, a ray whose opacity sits
     near the 0.95 threshold, or a leading empty-space test can fall the other way when the filtered value moves by 1/256 of
     a voxel difference - that changes a whole sample's contribution):
-        <= 2 LSB on >= TOL_EDGY_WITHIN2 of the pixels; the maximum is reported, not bounded (one flipped first-hit sample
-        of an opaque TF changes a pixel completely)
+        <= 2 LSB on >= TOL_EDGY_WITHIN2 and <= 4 LSB on >= TOL_EDGY_WITHIN4 of the pixels; the maximum is reported, not bounded
+        (one flipped first-hit sample of an opaque TF changes a pixel completely; measured: 4..28 LSB with the default TF, 111
+        with the opaque one)
 
 and, as the discriminating control, the nearest-neighbour parity policy is much farther from GPURenderer4 than either
 trilinear policy on the same frames."""
@@ -25,11 +26,11 @@ import oracle
 from common import golden_scene
 
 TOL_SMOOTH_WITHIN1, TOL_SMOOTH_MAX = 0.999, 2
-TOL_EDGY_WITHIN2 = 0.97
+TOL_EDGY_WITHIN2, TOL_EDGY_WITHIN4 = 0.97, 0.98   # measured minima: 0.9807 / 0.9827 (synthB64_opaque_ortho)
 
 SMOOTH = ["synthA64_semi_ortho", "synthA64_semi_persp"]
 EDGY = ["bucky_ortho_0_0_0", "bucky_persp_-45_-45_0", "bucky_ortho_90_0_0", "synthA64_default_ortho", "synthA64_default_persp",
-        "synthA96_default_step1.7", "synthB64_default_noesl", "synthB64_default_thr1_kd0"]
+        "synthA96_default_step1.7", "synthB64_default_noesl", "synthB64_default_thr1_kd0", "synthB64_opaque_ortho", "synthB64_opaque_persp"]
 
 
 def _compare(name, golden, port, volumes, R):
@@ -62,5 +63,5 @@ def test_trilinear_policies_match_gpurenderer4_with_decisions(name, golden, port
     record_property("lsb_histograms", rep)
     for sampler in ("trilinear", "trilinear-fma"):
         r = rep[sampler]
-        assert r["within2"] >= TOL_EDGY_WITHIN2, (name, sampler, r)
+        assert r["within2"] >= TOL_EDGY_WITHIN2 and r["within4"] >= TOL_EDGY_WITHIN4, (name, sampler, r)
         assert sum(r["mean_abs_per_channel"]) < sum(rep["hybridw"]["mean_abs_per_channel"]), (name, sampler)

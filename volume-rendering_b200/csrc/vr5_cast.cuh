@@ -31,7 +31,7 @@ constexpr int kWindowGuard = 8;   // guard voxels around the window layout (spec
 // 6 resident CTAs per SM (40 registers) measured best for the window variants (44 registers / 5 CTAs: 0.631 ms per C3 frame,
 // 40 / 6: 0.617, 36 / 7: 0.717 - profiles/r01_sampler_choice.md). 0 = no minimum for the others.
 #ifndef VR5_MIN_CTAS
-#define VR5_MIN_CTAS (SAMPLER >= 4 ? 6 : 0)
+#define VR5_MIN_CTAS (SAMPLER >= 2 ? 6 : 0)
 #endif
 
 // Kernel variant ids (template parameter SAMPLER): 0..6 are the public VR5_SAMPLER_* policies. 7..9 are the power-of-two
@@ -50,7 +50,10 @@ struct Counters {
 // persistent grid pulls the tiles of all frames of the sequence from ONE queue (frame = slot / n_queue), so a launch has one
 // tail however many frames it renders, and the host submits a whole camera path with one call. 80 bytes, 16-byte aligned.
 struct FrameView {
-    float ox, oy, oz, dx, dy, dz, rx, ry, rz, ux, uy, uz;  // origin, direction, right_plane, up_plane of the frame's View
+    // direction, origin, right_plane, up_plane of the frame's View. The direction comes first: the kernel reads the record as
+    // three 16-byte vectors, and (dx, dy) must land in an even-aligned register pair - the march multiplies it as one packed
+    // operand; at offsets 3 and 4 the pair straddled two vector loads and cost two register moves per march step
+    float dx, dy, dz, ox, oy, oz, rx, ry, rz, ux, uy, uz;
     uchar4 *out;               // the frame's buffer (a slot of a frame ring, possibly in a peer GPU's memory)
     // frame-ring hand-shake (vr5_peer.cu), both optional:
     uint32_t *arrive;          // += 1 (system scope, behind a system fence) by the warp that finishes this rank's last tile of the frame
@@ -67,6 +70,7 @@ struct KArgs {
     uint32_t n_frames;
     uint32_t *frame_done;    // sequence with hand-shake: queue slots finished per frame (zeroed before the launch)
     uint32_t *timed_out;     // set when a wait for `consumed` gives up (bounded: a missing consumer must not hang the GPU)
+    int ring_remote;         // the frames' buffers lie in a peer GPU's memory (system-scope fences before a slot is counted)
     // view (ViewBase.h:14-21)
     float ox, oy, oz;        // origin
     float dx, dy, dz;        // direction
@@ -241,10 +245,128 @@ __device__ __forceinline__ uint32_t div_block(const KArgs &a, uint32_t idx) {
 
 template <int V> struct FetchTag { static constexpr int value = V; };
 
+// ---- leading empty-space loop (CPURenderer.cpp:18-25; sample_data_esl RaycasterBase.h:52-65; leap RaycasterBase.h:67-85) ----
+// One iteration of the reference costs four IEEE divisions, three float->int and three int->float conversions and a floor:
+// eleven operations of the conversion / special-function unit (a fraction of the fp32 rate), on a chain that an opaque
+// transfer function runs about twice per sample (BASELINE configs[3]). The leap only enters the ray parameter as
+//     k += floor(max(min(kx, ky, kz), 0) / step) * step,          kx = ((min_bound + block_size * bx) - p.x) / d.x, ...
+// i.e. through the INTEGER m = floor(.): the quotients themselves never reach k. PREDICT = true therefore predicts m with
+// reciprocal multiplications (y = RN(1 / d) per ray, one rounding each, relative error of x~ = dk / step against the
+// reference's correctly rounded chain below 2^-21: three roundings of at most 2^-24 on the quotient that attains the minimum -
+// signs and zeros are exact, so max(., 0) agrees - one on 1 / step, one on the product, one on each reference quotient) and
+// ACCEPTS the prediction only when x~ is farther than x~ * 2^-19 from both neighbouring integers - then no integer can lie
+// between x~ and the reference's x, and floor agrees. Otherwise (and for NaN / inf, which fail the test by construction) the
+// lane redoes the iteration with the reference's divisions. Voxel indices come out of the mantissa of (v + 2^23) rounded
+// toward zero (exact for -2^22 < v < 2^22; a slightly negative v gives -1, clamped to 0 like the saturating conversion), block
+// indices go back to float through the same constant (exact: they are < 2^16). The host enables PREDICT only for finite
+// views clipped to [-1, 1]^3 (every point of the loop lies in the cube up to rounding, so |v| <= n + 1), the ray enables it
+// only when its non-zero direction components and the step lie in [2^-60, 2^60] (no reciprocal under- or overflows).
+// What the loop leaves in k, p is bit for bit what the reference's loop leaves: tests/test_gpu_parity.py, test_gpu_full_size.py.
+__device__ __forceinline__ uint32_t magic_voxel(float p, float half_n, uint32_t n_minus_1) {
+    const int i = (int)(__float_as_uint(__fadd_rz(fmul(fadd(p, 1.0f), half_n), 8388608.0f)) - 0x4B000000u);
+    return (uint32_t)min(max(i, 0), (int)n_minus_1);
+}
+__device__ __forceinline__ float small_uint_to_float(uint32_t b) { return fsub(__uint_as_float(0x4B000000u + b), 8388608.0f); }  // exact for b < 2^23
+__device__ __forceinline__ bool recip_safe(float d) {  // 0, or 2^-60 <= |d| <= 2^60
+    const uint32_t e = (__float_as_uint(d) >> 23) & 0xffu;
+    return d == 0.0f || (e >= 127u - 60u && e <= 127u + 60u);
+}
+
+// what the predicted loop reads per iteration, staged in shared memory by the kernel and read back through a volatile
+// pointer at loop entry: that pins the values in registers for the loop (ptxas otherwise re-loads every one of them from the
+// constant bank in every iteration, one issue slot each) without keeping them alive across the march
+struct EslPin { float bsx, bsy, bsz, hx, hy, hz; uint32_t nx1, ny1, nz1, bd_magic; };
+__device__ __forceinline__ EslPin make_esl_pin(const KArgs &a) { return EslPin{a.bsx, a.bsy, a.bsz, a.hx, a.hy, a.hz, a.nx1, a.ny1, a.nz1, a.bd_magic}; }
+
+// returns false when the ray leaves its clip interval without meeting a non-empty block (the reference returns without writing)
+#ifndef VR5_ESL_INLINE
+#define VR5_ESL_INLINE __forceinline__
+#endif
+template <bool COUNT, bool FMA>
+__device__ VR5_ESL_INLINE bool skip_leading_empty_space(const KArgs &a, const EslPin *pin_shared, const uint32_t *esl_bits, float step, float ox, float oy,
+                                                         float oz, float dx, float dy, float dz, float &k, float k_far, float &px, float &py, float &pz,
+                                                         Counters &cnt) {
+    auto point = [&](float o, float d, float kk) { return FMA ? __fmaf_rn(d, kk, o) : fadd(o, fmul(d, kk)); };
+    const float hx = a.hx, hy = a.hy, hz = a.hz;
+    {   // most rays of a dense volume start in a non-empty block: test the first point before setting the loop up
+        const uint32_t bx = div_block(a, world_to_voxel(px, hx, a.nx1)), by = div_block(a, world_to_voxel(py, hy, a.ny1)), bz = div_block(a, world_to_voxel(pz, hz, a.nz1));
+        if (k <= k_far && ((esl_bits[(bz * 32u + by) & 1023u] >> (bx & 31u)) & 1u) == 0u) return true;
+    }
+#ifndef VR5_NO_ESL_PREDICT
+    if (a.esl == 2 && recip_safe(dx) && recip_safe(dy) && recip_safe(dz)) {
+        // (a.esl == 2: the host has checked the view, the step and the block edge, and min_bound == -1: vr5_render.cu fill_args)
+        const volatile EslPin *pv = pin_shared;
+        const float bsx = pv->bsx, bsy = pv->bsy, bsz = pv->bsz, phx = pv->hx, phy = pv->hy, phz = pv->hz;
+        const int nx1 = (int)pv->nx1, ny1 = (int)pv->ny1, nz1 = (int)pv->nz1;
+        const uint32_t bd_magic = pv->bd_magic, esl_addr = (uint32_t)__cvta_generic_to_shared(esl_bits);
+        // prediction constants per axis: quotient ~ n * y + c with (y, c) = (RN(1 / d), 0), or (0, 100) for a zero component
+        const float yx = dx == 0.0f ? 0.0f : __frcp_rn(dx), yy = dy == 0.0f ? 0.0f : __frcp_rn(dy), yz = dz == 0.0f ? 0.0f : __frcp_rn(dz);
+        const float cx = dx == 0.0f ? 100.0f : 0.0f, cy = dy == 0.0f ? 100.0f : 0.0f, cz = dz == 0.0f ? 100.0f : 0.0f;
+        const float ys = __frcp_rn(step);
+        // block index + (d > 0) goes back to float through the 2^23 bias: one integer add, one exact subtraction
+        const uint32_t ux = 0x4B000000u + (dx > 0.0f ? 1u : 0u), uy = 0x4B000000u + (dy > 0.0f ? 1u : 0u), uz = 0x4B000000u + (dz > 0.0f ? 1u : 0u);
+        auto voxel = [](float p, float half_n, int n1) {   // magic_voxel with pinned operands
+            return (uint32_t)min(max((int)(__float_as_uint(__fadd_rz(fmul(fadd(p, 1.0f), half_n), 8388608.0f)) - 0x4B000000u), 0), n1);
+        };
+        while (k <= k_far) {
+            const uint32_t bx = __umulhi(voxel(px, phx, nx1), bd_magic), by = __umulhi(voxel(py, phy, ny1), bd_magic), bz = __umulhi(voxel(pz, phz, nz1), bd_magic);
+            uint32_t word;
+            asm("ld.shared.u32 %0, [%1];" : "=r"(word) : "r"(esl_addr + (((bz << 5) + by) & 1023u) * 4u));
+            if (((word >> (bx & 31u)) & 1u) == 0u) break;
+            const float nx = fsub(fadd(-1.0f, fmul(bsx, fsub(__uint_as_float(bx + ux), 8388608.0f))), px);
+            const float ny = fsub(fadd(-1.0f, fmul(bsy, fsub(__uint_as_float(by + uy), 8388608.0f))), py);
+            const float nz = fsub(fadd(-1.0f, fmul(bsz, fsub(__uint_as_float(bz + uz), 8388608.0f))), pz);
+            // prediction (not part of the bit-exact chain: any arithmetic will do, only the error bound above matters)
+            const float x = fmaxf(fminf(fminf(__fmaf_rn(nx, yx, cx), __fmaf_rn(ny, yy, cy)), __fmaf_rn(nz, yz, cz)), 0.0f) * ys;
+            float mf = fsub(__fadd_rz(x, 8388608.0f), 8388608.0f);  // floor(x) for 0 <= x < 2^23
+            if (!(__fmaf_rn(x, 0x1p-19f, fabsf(fsub(fsub(x, mf), 0.5f))) <= 0.5f)) {
+                // too close to an integer (or not finite): the reference's own arithmetic decides
+                float kx = fdiv(nx, dx), ky = fdiv(ny, dy), kz = fdiv(nz, dz);
+                if (dx == 0.0f) kx = 100.0f;
+                if (dy == 0.0f) ky = 100.0f;
+                if (dz == 0.0f) kz = 100.0f;
+                mf = floorf(fdiv(sel_max(sel_min(sel_min(kx, ky), kz), 0.0f), step));
+            }
+            k = fadd(k, fmul(mf, step));
+            if (COUNT) cnt.esl_iters++;
+            k = fadd(k, step);
+            px = point(ox, dx, k); py = point(oy, dy, k); pz = point(oz, dz, k);
+        }
+    } else
+#endif
+    {
+        while (k <= k_far) {
+            uint32_t bx = div_block(a, world_to_voxel(px, hx, a.nx1));
+            uint32_t by = div_block(a, world_to_voxel(py, hy, a.ny1));
+            uint32_t bz = div_block(a, world_to_voxel(pz, hz, a.nz1));
+            const uint32_t word = esl_bits[(bz * 32u + by) & 1023u];
+            if (((word >> (bx & 31u)) & 1u) == 0u) break;
+            if (dx > 0.0f) bx++;
+            if (dy > 0.0f) by++;
+            if (dz > 0.0f) bz++;
+            float kx = fdiv(fsub(fadd(a.mbx, fmul(a.bsx, (float)bx)), px), dx);
+            float ky = fdiv(fsub(fadd(a.mby, fmul(a.bsy, (float)by)), py), dy);
+            float kz = fdiv(fsub(fadd(a.mbz, fmul(a.bsz, (float)bz)), pz), dz);
+            if (dx == 0.0f) kx = 100.0f;
+            if (dy == 0.0f) ky = 100.0f;
+            if (dz == 0.0f) kz = 100.0f;
+            float dk = sel_min(kx, ky);
+            dk = sel_min(dk, kz);
+            dk = sel_max(dk, 0.0f);
+            dk = fmul(floorf(fdiv(dk, step)), step);
+            k = fadd(k, dk);
+            if (COUNT) cnt.esl_iters++;
+            k = fadd(k, step);
+            px = point(ox, dx, k); py = point(oy, dy, k); pz = point(oz, dz, k);
+        }
+    }
+    return !(k > k_far);
+}
+
 // ---- one ray (CPURenderer.cpp:11-41). Returns the packed RGBA8 pixel; 0 when the reference leaves it cleared. ----
 template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
 __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, const VolScale &vs, const Window &win, uint32_t lut_addr, const uint32_t *esl_bits,
-                                             float step, float threshold, int col, int row, Counters &cnt) {
+                                             const EslPin *esl_pin, float step, float threshold, int col, int row, Counters &cnt) {
     // View::get_ray (ViewBase.h:23-35)
     const float cx = (float)(col - a.half_w);
     const float cy = (float)(row - a.half_h);
@@ -276,34 +398,8 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
     if (COUNT) cnt.rays_hit++;
     float px = fadd(ox, fmul(dx, k)), py = fadd(oy, fmul(dy, k)), pz = fadd(oz, fmul(dz, k));
 
-    // leading empty-space loop (CPURenderer.cpp:18-25; sample_data_esl RaycasterBase.h:52-65; leap RaycasterBase.h:67-85)
-    if (a.esl) {
-        while (k <= k_far) {
-            uint32_t bx = div_block(a, world_to_voxel(px, vs.hx, a.nx1));
-            uint32_t by = div_block(a, world_to_voxel(py, vs.hy, a.ny1));
-            uint32_t bz = div_block(a, world_to_voxel(pz, vs.hz, a.nz1));
-            const uint32_t word = esl_bits[(bz * 32u + by) & 1023u];
-            if (((word >> (bx & 31u)) & 1u) == 0u) break;
-            if (dx > 0.0f) bx++;
-            if (dy > 0.0f) by++;
-            if (dz > 0.0f) bz++;
-            float kx = fdiv(fsub(fadd(a.mbx, fmul(a.bsx, (float)bx)), px), dx);
-            float ky = fdiv(fsub(fadd(a.mby, fmul(a.bsy, (float)by)), py), dy);
-            float kz = fdiv(fsub(fadd(a.mbz, fmul(a.bsz, (float)bz)), pz), dz);
-            if (dx == 0.0f) kx = 100.0f;
-            if (dy == 0.0f) ky = 100.0f;
-            if (dz == 0.0f) kz = 100.0f;
-            float dk = sel_min(kx, ky);
-            dk = sel_min(dk, kz);
-            dk = sel_max(dk, 0.0f);
-            dk = fmul(floorf(fdiv(dk, step)), step);
-            k = fadd(k, dk);
-            if (COUNT) cnt.esl_iters++;
-            k = fadd(k, step);
-            px = fadd(ox, fmul(dx, k)); py = fadd(oy, fmul(dy, k)); pz = fadd(oz, fmul(dz, k));
-        }
-        if (k > k_far) return 0u;
-    }
+    // leading empty-space loop
+    if (a.esl && !skip_leading_empty_space<COUNT, false>(a, esl_pin, esl_bits, step, ox, oy, oz, dx, dy, dz, k, k_far, px, py, pz, cnt)) return 0u;
     if (COUNT) cnt.rays_accum++;
 
     // accumulation loop (CPURenderer.cpp:28-39), software pipelined: the voxel of sample i+1 is requested before sample i
@@ -311,7 +407,11 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
     // speculative (it may lie beyond k_far; clamped index or padded texture make it harmless) and changes no result.
     if (!(k <= k_far)) return 0u;  // NaN interval: the reference writes an all-zero pixel
     float ar = 0.0f, ag = 0.0f, ab = 0.0f, aa = 0.0f;
-    const f32x2 dxy = pack2(dx, dy), hxy = pack2(vs.hx, vs.hy), one2 = pack2(1.0f, 1.0f);
+    // (dx, dy) as ONE value the compiler cannot see through: left to itself the allocator keeps the two scalars of the ray set-up
+    // in unrelated registers and re-pairs them with two moves in every march step
+    f32x2 dxy = pack2(dx, dy);
+    asm volatile("" : "+l"(dxy));
+    const f32x2 hxy = pack2(vs.hx, vs.hy), one2 = pack2(1.0f, 1.0f);
     constexpr int S0 = SAMPLER >= 3 ? 2 : SAMPLER;  // hybrids / window: first sample and shading samples come from the texture
     // voxel of the sample at ray parameter kq; FETCH selects the memory path (2 = texture, 0 = linear / padded linear, 4 = window,
     // 5 / 6 = power-of-two window / texture). Speculative: kq may lie up to kPrefetch steps past k_far.
@@ -335,7 +435,8 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
                 uint32_t lo;
                 asm("{\n\t.reg .u32 t;\n\tmad.lo.u32 t, %2, %4, %1;\n\tmad.lo.u32 %0, %3, %5, t;\n\t}"
                     : "=r"(lo) : "r"(bx), "r"(by), "r"(bz), "r"(win.sx), "r"(win.sxy));
-                asm("{\n\t.reg .u64 p;\n\tmov.b64 p, {%1, %2};\n\tld.global.nc.u8 %0, [p];\n\t}" : "=r"(sn) : "r"(lo), "r"(win.hi));
+                // 64-bit window base (uniform) + 32-bit offset: one LDG with a uniform-register base, no register pair to assemble
+                sn = __ldg(reinterpret_cast<const uint8_t *>((uint64_t)win.hi << 32) + lo);
             } else {           // texture: strip the exponent field, coordinate = index + kP2Origin
                 uint32_t r0, r1, r2, r3;
                 asm("tex.3d.v4.u32.s32 {%0, %1, %2, %3}, [%4, {%5, %6, %7, %8}];"
@@ -487,24 +588,37 @@ __device__ __forceinline__ uint32_t load_acquire_sys_u32(const uint32_t *p) {
     return v;
 }
 
-// view of frame f: kernel parameters for a single frame, the device array for a sequence (uniform loads, once per tile;
-// nothing of it stays live across the march)
-__device__ __forceinline__ RayView load_view(const KArgs &a, uint32_t f) {
+// view of the tile's frame: kernel parameters for a single frame; for a sequence the warp's shared-memory copy of the frame's
+// record (refreshed when the warp moves on to another frame: run_tile_queue). Once per tile; nothing of it stays live across
+// the march.
+__device__ __forceinline__ RayView load_view(const KArgs &a, const FrameView *cached) {
     if (a.frames) {
-        const float4 *p = reinterpret_cast<const float4 *>(a.frames + f);
-        const float4 x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
-        return RayView{x.x, x.y, x.z, x.w, y.x, y.y, y.z, y.w, z.x, z.y, z.z, z.w};
+        const float4 *p = reinterpret_cast<const float4 *>(cached);
+        const float4 x = p[0], y = p[1], z = p[2];
+        return RayView{x.w, y.x, y.y, x.x, x.y, x.z, y.z, y.w, z.x, z.y, z.z, z.w};
     }
     return RayView{a.ox, a.oy, a.oz, a.dx, a.dy, a.dz, a.rx, a.ry, a.rz, a.ux, a.uy, a.uz};
 }
 
-// `count` queue slots of frame f are finished (their pixels stored and fenced): the warp that completes the frame's last slot
+// Memory ordering of the frame-ring hand-shake. A warp's pixel stores must be visible to whoever observes the rank's arrival:
+//   lanes store pixels -> warp / CTA barrier -> ONE thread: fence, then atomicAdd on the frame's slot counter (device scope)
+//   the thread whose add completes the frame: fence (system scope), then the system-scope arrival.
+// The fences are cumulative, so the one thread's fence covers the other lanes' stores it is ordered behind by the barrier. For a
+// ring in a PEER GPU's memory (a.ring_remote) the first fence is a system-scope one as well: the pixels travel over NVLink and a
+// device-scope fence says nothing about their arrival there.
+__device__ __forceinline__ void ring_fence(bool system_scope) {
+    if (system_scope) asm volatile("fence.acq_rel.sys;" ::: "memory");
+    else asm volatile("fence.acq_rel.gpu;" ::: "memory");
+}
+
+// `count` queue slots of frame f are finished (pixels stored, barrier passed): count them; the add that completes the frame
 // publishes the rank's arrival in the frame ring. Called by one thread.
 __device__ __forceinline__ void frame_slots_done(const KArgs &a, uint32_t f, uint32_t count) {
+    ring_fence(a.ring_remote != 0);
     if (atomicAdd(a.frame_done + f, count) + count == a.n_queue) {
         const FrameView &fv = a.frames[f];
         if (fv.arrive) {
-            __threadfence_system();
+            ring_fence(true);
             atomicAdd_system(fv.arrive, 1u);
         }
     }
@@ -513,9 +627,9 @@ __device__ __forceinline__ void frame_slots_done(const KArgs &a, uint32_t f, uin
 // The slot of frame f may be written once the consumer has released the frame that used it before. Frames are released in
 // order, so one shared "highest frame known to be writable" per CTA saves all but the first poll of a frame. Bounded: after
 // 4 s the wait gives up, raises the status flag and the frame is written anyway (a lost consumer must not hang the device).
-__device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, volatile uint32_t *s_ok) {
+__device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, const FrameView *cached, volatile uint32_t *s_ok) {
     if (*s_ok != 0xffffffffu && *s_ok >= f) return;
-    const FrameView &fv = a.frames[f];
+    const FrameView &fv = *cached;
     if (fv.consumed) {
         unsigned long long t0;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -532,16 +646,34 @@ __device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, 
 // ray(view, col, row) -> RGBA8 pixel. COUNT: instrumented pass, nothing is stored.
 template <bool COUNT, class RayFn>
 __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ unsigned s_q;
-    __shared__ uint32_t s_ok;   // sequence hand-shake: highest frame whose slot is known to be writable (0xffffffff: none yet)
-    const bool shake = a.frames && a.frame_done;
+    __shared__ uint32_t s_ok;          // sequence hand-shake: highest frame whose slot is known to be writable (0xffffffff: none yet)
+    // finished queue slots are counted per frame, and a warp (CTA with CTA-wide fetch) adds its share to the frame's counter
+    // ONCE, when it moves on to another frame or leaves: [w][0] = frame being counted (0xffffffff: none), [w][1] = slots
+    __shared__ uint32_t s_acc[kCtaThreads / 32][2];
+    // sequence: the record of the frame a warp is working on (view, buffer, hand-shake words) and which frame that is
+    __shared__ __align__(16) FrameView s_view[kCtaThreads / 32];
+    __shared__ uint32_t s_view_f[kCtaThreads / 32];
+    if (a.frames) {
+        if (lane == 0) s_view_f[warp] = 0xffffffffu;
+        __syncwarp();
+    }
+    const bool shake = !COUNT && a.frames && a.frame_done;
     if (shake) {
         if (threadIdx.x == 0) s_ok = 0xffffffffu;
+        if (lane == 0) { s_acc[warp][0] = 0xffffffffu; s_acc[warp][1] = 0u; }
         __syncthreads();
     }
     const uint32_t n_total = a.n_queue * a.n_frames;
-    uint32_t f_prev = 0xffffffffu;   // CTA fetch: frame of the block this CTA has just finished
+    // the slots this warp (lane 0) / CTA (thread 0) has just finished go to the account; the account is flushed when the next
+    // slot belongs to another frame or the queue is exhausted
+    auto account = [&](uint32_t finished, uint32_t q_next) {
+        const uint32_t f_next = q_next < n_total ? q_next / a.n_queue : 0xffffffffu;
+        uint32_t f_acc = s_acc[warp][0], n_acc = s_acc[warp][1] + (f_acc != 0xffffffffu ? finished : 0u);
+        if (f_acc != 0xffffffffu && f_acc != f_next) { frame_slots_done(a, f_acc, n_acc); n_acc = 0u; }
+        s_acc[warp][0] = f_next; s_acc[warp][1] = n_acc;
+    };
     for (;;) {
         unsigned q = 0;
         if (a.cta_fetch) {
@@ -550,42 +682,56 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
             // barrier per block, so the host only asks for it when rays of neighbouring tiles end together (no opaque TF
             // entry: C4 measured 5 % slower with it). Same counter arithmetic as one slot per warp.
             __syncthreads();
-            if (threadIdx.x == 0) {
-                if (shake && f_prev != 0xffffffffu) frame_slots_done(a, f_prev, (uint32_t)(kCtaThreads / 32));
-                s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
-            }
+            if (threadIdx.x == 0) s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
             __syncthreads();
+            if (shake && threadIdx.x == 0) account((uint32_t)(kCtaThreads / 32), s_q);   // behind the barrier: the other warps are marching already
             q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
         } else {
-            if (lane == 0) q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
+            if (shake) __syncwarp();       // the lanes' stores of the previous tile are ordered before lane 0's accounting
+            if (lane == 0) {
+                q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
+                if (shake) account(1u, q);
+            }
             q = __shfl_sync(0xffffffffu, q, 0);
         }
         if (q >= n_total) break;
         uint32_t f = 0, qi = q;
-        if (a.frames) { f = q / a.n_queue; qi = q - f * a.n_queue; }   // a block of 8 never straddles frames (n_queue % 32 == 0)
-        f_prev = f;
-        if (shake && !COUNT) {   // before the march: the frame's slot is almost always free long since
-            if (lane == 0) wait_frame_writable(a, f, &s_ok);
-            __syncwarp();
-        }
-        uint32_t tx, tyl;
-        tile_of_slot(a, qi, tx, tyl);
-        const int col = (int)tx * kTileW + (lane & 7);
-        const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
-        if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {  // ragged edges: lanes outside the image idle
-            const RayView v = load_view(a, f);
-            const uint32_t rgba = ray(v, col, row);
-            if (!COUNT) {
-                uchar4 *out = a.frames ? a.frames[f].out : a.out;
-                const int out_row = a.packed ? (int)tyl * kTileH + (lane >> 3) : row;
-                reinterpret_cast<uint32_t *>(out)[(size_t)out_row * a.width + col] = rgba;
+        if (a.frames) {
+            f = q / a.n_queue; qi = q - f * a.n_queue;   // a block of 8 never straddles frames (n_queue % 32 == 0)
+            if (s_view_f[warp] != f) {                   // first tile of this warp in frame f: fetch the frame's record (80 bytes)
+                __syncwarp();
+                if (lane < (int)(sizeof(FrameView) / 4)) reinterpret_cast<uint32_t *>(&s_view[warp])[lane] = __ldg(reinterpret_cast<const uint32_t *>(a.frames + f) + lane);
+                if (lane == 0) s_view_f[warp] = f;
+                __syncwarp();
             }
         }
-        if (shake) {
-            __threadfence_system();   // this lane's pixels are visible system-wide before the slot is counted
-            if (!a.cta_fetch) {
-                __syncwarp();
-                if (lane == 0) frame_slots_done(a, f, 1u);
+        if (shake) {   // before the march: the frame's slot is almost always free long since
+            if (lane == 0) wait_frame_writable(a, f, &s_view[warp], &s_ok);
+            __syncwarp();
+        }
+        uint32_t rgba = 0u;
+        {
+            uint32_t tx, tyl;
+            tile_of_slot(a, qi, tx, tyl);
+            const int col = (int)tx * kTileW + (lane & 7);
+            const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
+            if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height)  // ragged edges: lanes outside the image idle
+                rgba = ray(load_view(a, &s_view[warp]), col, row);
+        }
+        if (!COUNT) {
+            // Only the queue slot survives the march: the pixel's place is worked out AGAIN from it (a few dozen instructions per
+            // tile) instead of keeping tile coordinates, frame index and buffer address in registers through the march loop,
+            // where every register counts (40 per thread for six resident CTAs per SM).
+            asm volatile("" : "+r"(qi));
+            uint32_t tx, tyl;
+            tile_of_slot(a, qi, tx, tyl);
+            const int lane2 = threadIdx.x & 31;
+            const int col = (int)tx * kTileW + (lane2 & 7);
+            const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane2 >> 3);
+            if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {
+                uchar4 *out = a.frames ? s_view[threadIdx.x >> 5].out : a.out;
+                const int out_row = a.packed ? (int)tyl * kTileH + (lane2 >> 3) : row;
+                reinterpret_cast<uint32_t *>(out)[(size_t)out_row * a.width + col] = rgba;
             }
         }
     }
@@ -599,8 +745,10 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
     __shared__ float4 s_lut[256];
     __shared__ uint32_t s_esl[1024];
     __shared__ Pinned s_pinned;
+    __shared__ EslPin s_esl_pin;
     for (int i = threadIdx.x; i < 256; i += kCtaThreads) s_lut[i] = a.tf[i >> 1];
     for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
+    if (threadIdx.x == 32) s_esl_pin = make_esl_pin(a);
     if (threadIdx.x == 0) s_pinned = Pinned{a.hx, a.hy, a.hz, a.step, a.threshold, a.wmx, a.wmy, a.wmz, a.whi, a.wsx, a.wsxy};
     __syncthreads();
 
@@ -613,7 +761,7 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
     const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_lut);
     Counters cnt = {0, 0, 0, 0, 0};
     run_tile_queue<COUNT>(a, [&](const RayView &v, int col, int row) {
-        return cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, v, vs, win, lut_addr, s_esl, step, threshold, col, row, cnt);
+        return cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, v, vs, win, lut_addr, s_esl, &s_esl_pin, step, threshold, col, row, cnt);
     });
     if (COUNT) {
         unsigned long long v[5] = {cnt.rays_hit, cnt.rays_accum, cnt.esl_iters, cnt.samples, cnt.shaded};

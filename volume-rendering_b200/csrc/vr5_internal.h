@@ -93,6 +93,7 @@ struct vr5_renderer {
         bool tri_clamped = false;   // VR5_TRI_CLAMPED: trilinear march with clamped record indices
         int trif_ctas = 6;          // VR5_TRIF_CTAS: register budget of the contracted trilinear march (CTAs per SM)
         int trif_depth = 2;         // VR5_TRIF_DEPTH: cell requests in flight per ray
+        bool esl_exact = false;     // VR5_ESL_EXACT: the leading empty-space loop divides in every iteration (no predicted leaps)
         bool no_p2 = false;         // VR5_NO_P2: never build the power-of-two window
         uint32_t win_sx = 0;        // VR5_WIN_SX: row stride of the window layouts (0 = default)
     } opt;
@@ -119,7 +120,7 @@ struct vr5_frame_target {
     uint32_t consumed_target;
 };
 // async launch of ONE persistent kernel over frames[0..n) on the renderer's stream (vr5_render.cu)
-int vr5_sequence_launch(vr5_renderer *r, const struct vr5_params *frames, int n, const vr5_frame_target *targets, uint32_t *timed_out_dev);
+int vr5_sequence_launch(vr5_renderer *r, const struct vr5_params *frames, int n, const vr5_frame_target *targets, uint32_t *timed_out_dev, int targets_remote);
 
 #define VR5_CUDA(r, call)                                         \
     do {                                                          \

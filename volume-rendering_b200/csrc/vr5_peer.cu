@@ -260,7 +260,7 @@ extern "C" int vr5_peer_render_sequence(vr5_renderer *r, const vr5_params *frame
         const uint32_t use = (uint32_t)(seq / slots);
         t[(size_t)i] = vr5_frame_target{slot_ptr(r, seq), arrive_word(r->peer_base, slot), use ? consumed_word(r->peer_base, slot) : nullptr, use};
     }
-    return vr5_sequence_launch(r, frames, n, t.data(), timeout_word(r->peer_base));
+    return vr5_sequence_launch(r, frames, n, t.data(), timeout_word(r->peer_base), r->peer_owner ? 0 : 1);
 }
 
 // owner: consume frames seq0 .. seq0 + n - 1 in order, on the renderer's consumer stream (asynchronous; vr5_join / vr5_sync

@@ -233,7 +233,7 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     if ((e = cudaStreamCreateWithFlags(&r->consumer_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate consumer", e);
     if ((e = cudaEventCreateWithFlags(&r->consumer_done, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     // experiment knobs: the environment is read here, once; the launch path only looks at r->opt (vr5_set_option changes it)
-    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX"})
+    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX", "VR5_ESL_EXACT"})
         if (const char *v = getenv(name)) vr5_set_option(r, name, v);
     r->err.clear();
     const char *env = getenv("VR5_SAMPLER");
@@ -723,6 +723,7 @@ extern "C" int vr5_set_option(vr5_renderer *r, const char *name, const char *val
     else if (!strcmp(name, "VR5_TRI_CLAMPED")) r->opt.tri_clamped = truthy();
     else if (!strcmp(name, "VR5_TRIF_CTAS")) r->opt.trif_ctas = atoi(value);
     else if (!strcmp(name, "VR5_TRIF_DEPTH")) r->opt.trif_depth = atoi(value);
+    else if (!strcmp(name, "VR5_ESL_EXACT")) r->opt.esl_exact = truthy();
     else if (!strcmp(name, "VR5_NO_P2")) r->opt.no_p2 = truthy();        // takes effect at the next layout build
     else if (!strcmp(name, "VR5_WIN_SX")) r->opt.win_sx = (uint32_t)strtoul(value, nullptr, 10);
     else { vr5_fail(r, "vr5_set_option: unknown option", cudaSuccess, __FILE__, __LINE__); return 1; }
@@ -859,6 +860,13 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     }
     a->counters = reinterpret_cast<Counters *>(r->d_counters);
     a->reach = frame_reach(*a);
+    // predicted leaps (vr5_cast.cuh, skip_leading_empty_space): finite, non-degenerate view, rays clipped to the cube [-1, 1]^3
+    // the grid fills, step with a safe reciprocal; VR5_ESL_EXACT keeps the reference's divisions in every iteration
+    int step_exp = 0;
+    frexpf(p->ray_step, &step_exp);
+    if (a->esl && !r->opt.esl_exact && std::isfinite(a->reach) && a->mbx == -1.0f && a->mby == -1.0f && a->mbz == -1.0f && step_exp > -60 && step_exp < 60 && bd >= 2 &&
+        std::isfinite(a->bsx) && std::isfinite(a->bsy) && std::isfinite(a->bsz))
+        a->esl = 2;
     return 0;
 }
 
@@ -905,7 +913,7 @@ static int launch(vr5_renderer *r, KArgs a, bool count, int lane) {
 // The tiles of every frame go through one queue (slot / n_queue = frame), so the grid idles behind its last long rays once per
 // sequence instead of once per frame, and the host submits the whole path with one call (VolR's benchmark loop renders its
 // frames one call at a time, VolR.cpp:98-113, :225-321). Everything but the camera must be the same for all frames.
-int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const vr5_frame_target *targets, uint32_t *timed_out_dev) {
+int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const vr5_frame_target *targets, uint32_t *timed_out_dev, int targets_remote) {
     if (!frames || !targets || n < 1) { vr5_fail(r, "vr5_render_sequence: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
     KArgs a;
     if (fill_args(r, frames, targets[0].out_dev, &a)) return 1;
@@ -927,7 +935,7 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
             a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
         }
         const vr5_view &v = p.view;
-        fv[i] = FrameView{v.origin.x, v.origin.y, v.origin.z, v.direction.x, v.direction.y, v.direction.z, v.right_plane.x, v.right_plane.y, v.right_plane.z,
+        fv[i] = FrameView{v.direction.x, v.direction.y, v.direction.z, v.origin.x, v.origin.y, v.origin.z, v.right_plane.x, v.right_plane.y, v.right_plane.z,
                           v.up_plane.x, v.up_plane.y, v.up_plane.z, reinterpret_cast<uchar4 *>(targets[i].out_dev), targets[i].arrive, targets[i].consumed,
                           targets[i].consumed_target, 0u};
         shake |= targets[i].arrive || targets[i].consumed;
@@ -943,6 +951,7 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
     a.n_frames = (uint32_t)n;
     a.frame_done = shake ? reinterpret_cast<uint32_t *>(blk + views_bytes) : nullptr;
     a.timed_out = timed_out_dev;
+    a.ring_remote = targets_remote ? 1 : 0;
     a.queue = r->d_seq_queue;
     a.queue_base = r->seq_queue_base;
     r->launch_stream = st;
@@ -959,7 +968,7 @@ extern "C" int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, in
     VR5_CUDA(r, cudaSetDevice(r->device));
     std::vector<vr5_frame_target> t((size_t)n_frames);
     for (int i = 0; i < n_frames; i++) t[(size_t)i] = vr5_frame_target{outs_dev[i], nullptr, nullptr, 0u};
-    return vr5_sequence_launch(r, frames, n_frames, t.data(), nullptr);
+    return vr5_sequence_launch(r, frames, n_frames, t.data(), nullptr, 0);
 }
 
 static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {

@@ -223,7 +223,7 @@ __device__ __forceinline__ void trif_classify(uint32_t pair_c, float v, float2 &
 }
 
 template <bool COUNT, bool FAST, bool SHADE, bool FMA, int DEPTH>
-__device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &rv, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, int col, int row,
+__device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &rv, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, const EslPin *esl_pin, int col, int row,
                                                  Counters &cnt) {
     // View::get_ray, Raycaster::intersect and the leading empty-space loop are those of the nearest path (vr5_cast.cuh)
     const float cx = (float)(col - a.half_w), cy = (float)(row - a.half_h);
@@ -252,31 +252,7 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &
     if (COUNT) cnt.rays_hit++;
     float px = ray_point<FMA>(ox, dx, k), py = ray_point<FMA>(oy, dy, k), pz = ray_point<FMA>(oz, dz, k);
     const float step = g.step;
-    if (a.esl) {
-        while (k <= k_far) {
-            uint32_t bx = div_block(a, world_to_voxel(px, a.hx, a.nx1));
-            uint32_t by = div_block(a, world_to_voxel(py, a.hy, a.ny1));
-            uint32_t bz = div_block(a, world_to_voxel(pz, a.hz, a.nz1));
-            const uint32_t word = esl_bits[(bz * 32u + by) & 1023u];
-            if (((word >> (bx & 31u)) & 1u) == 0u) break;
-            if (dx > 0.0f) bx++;
-            if (dy > 0.0f) by++;
-            if (dz > 0.0f) bz++;
-            float kx = fdiv(fsub(fadd(a.mbx, fmul(a.bsx, (float)bx)), px), dx);
-            float ky = fdiv(fsub(fadd(a.mby, fmul(a.bsy, (float)by)), py), dy);
-            float kz = fdiv(fsub(fadd(a.mbz, fmul(a.bsz, (float)bz)), pz), dz);
-            if (dx == 0.0f) kx = 100.0f;
-            if (dy == 0.0f) ky = 100.0f;
-            if (dz == 0.0f) kz = 100.0f;
-            float dk = sel_max(sel_min(sel_min(kx, ky), kz), 0.0f);
-            dk = fmul(floorf(fdiv(dk, step)), step);
-            k = fadd(k, dk);
-            if (COUNT) cnt.esl_iters++;
-            k = fadd(k, step);
-            px = ray_point<FMA>(ox, dx, k); py = ray_point<FMA>(oy, dy, k); pz = ray_point<FMA>(oz, dz, k);
-        }
-        if (k > k_far) return 0u;
-    }
+    if (a.esl && !skip_leading_empty_space<COUNT, FMA>(a, esl_pin, esl_bits, step, ox, oy, oz, dx, dy, dz, k, k_far, px, py, pz, cnt)) return 0u;
     if (COUNT) cnt.rays_accum++;
     if (!(k <= k_far)) return 0u;
     if (FMA) {
@@ -398,6 +374,8 @@ template <bool COUNT, bool FAST, bool SHADE, bool FMA, int MINB = (SHADE ? 0 : 6
 __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
     __shared__ float4 s_pair[2][kTriPairs];  // [0]: entries, [1]: differences to the next entry
     __shared__ uint32_t s_esl[1024];
+    __shared__ EslPin s_esl_pin;
+    if (threadIdx.x == 32) s_esl_pin = make_esl_pin(a);
     for (int i = threadIdx.x; i < kTriPairs; i += kCtaThreads) {
         const float4 lo = a.tf[min(max(i - 1, 0), 127)], hi = a.tf[min(i, 127)];
         s_pair[0][i] = lo;
@@ -418,7 +396,7 @@ __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_con
 #endif
     Counters cnt = {0, 0, 0, 0, 0};
     run_tile_queue<COUNT>(a, [&](const RayView &v, int col, int row) {
-        return cast_ray_tri<COUNT, FAST, SHADE, FMA, DEPTH>(a, v, t, g, s_esl, col, row, cnt);
+        return cast_ray_tri<COUNT, FAST, SHADE, FMA, DEPTH>(a, v, t, g, s_esl, &s_esl_pin, col, row, cnt);
     });
     if (COUNT) {
         unsigned long long v[5] = {cnt.rays_hit, cnt.rays_accum, cnt.esl_iters, cnt.samples, cnt.shaded};
