@@ -23,15 +23,23 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 # stdout carries exactly one JSON line. Libraries write there too (NCCL's version banner at communicator creation, the
-# reference's Logger), so file descriptor 1 is pointed at stderr for the life of the process and the line goes to the saved one.
-sys.stdout.flush()
-_JSON_FD = os.dup(1)
-os.dup2(2, 1)
+# reference's Logger), so main() points file descriptor 1 at stderr for the life of the process and the line goes to the saved
+# one. (Importing this module - tests, tools - leaves the descriptors alone.)
+_JSON_FD = None
+
+
+def claim_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
 
 
 def emit(line):
     sys.stdout.flush()
-    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+    os.write(_JSON_FD if _JSON_FD is not None else 1, (json.dumps(line) + "\n").encode())
+
 
 WORKLOADS = {  # BASELINE.json configs[1..4]
     "c2": dict(kind=0, n=256, seed=1, tf="semi", w=1920, h=1080, name="synthA 256^3 uint8, semi TF, 1920x1080, 360-frame orbit"),
@@ -231,7 +239,10 @@ def run_reference_arm(args, wl):
 # ---- this repo's arm ---------------------------------------------------------------------------------------------------
 def peer_slots(lanes):
     """Frame ring of the device-resident path: a producer may run this many frames ahead of the consumer (the per-frame
-    API needs a multiple of the frame lanes)."""
+    API needs a multiple of the frame lanes). VR5_RING_SLOTS overrides (profiling: ncu serialises kernels, so a sequence
+    kernel must not have to wait for its consumer - a ring at least as long as the sequence never makes it wait)."""
+    if os.environ.get("VR5_RING_SLOTS"):
+        return int(os.environ["VR5_RING_SLOTS"])
     return 8 if 8 % max(1, lanes) == 0 else 3 * lanes
 
 
@@ -377,16 +388,26 @@ def install_volume_from_file(ctx, gpu, path):
             "route": "rank 0 vr5_load_volume -> device buffer -> %s -> vr5_set_volume_device" % ("NCCL broadcast" if world > 1 else "same device")}
 
 
-def oracle_rows_check(wl, params_list, frames, rows, ctx, volume=None):
-    """rank 0: `rows` of each frame against the CPU checker (the reference's own code when it is prebuilt and its 32-bit
-    indices suffice, else the restated port): max LSB difference, rows checked."""
+def oracle_rows_check(wl, params_list, frames, rows, ctx, volume=None, sampler="hybridw"):
+    """rank 0: `rows` of each frame against the CPU checker: max LSB difference, rows checked. Nearest-neighbour policies: the
+    reference's own CPURenderer when it is prebuilt and its 32-bit indices suffice, else the restated port. Trilinear policies:
+    the matching section of the restated checker (their external anchor, GPURenderer4, needs a GPU: tests/test_trilinear_pin.py)."""
     cpu = CpuReference(wl, volume=volume)
+    tri = {"trilinear": "orc_render_rows_trilinear", "trilinear-fma": "orc_render_rows_trilinear_fma"}.get(sampler)
+    if tri:
+        cpu.kind = "port (%s section)" % sampler
     worst, checked = 0, 0
     for (ang, frame) in zip(params_list, frames):
         sc = cpu.scene(ang)
         out = np.zeros((wl["h"], wl["w"], 4), dtype=np.uint8)
         spans = [(r, r + 1) for r in rows]
-        cpu.render_rows(sc, out, spans, os.cpu_count() or 1)
+        if tri:
+            from concurrent.futures import ThreadPoolExecutor
+            fn = getattr(cpu.port.lib, tri)
+            with ThreadPoolExecutor(max_workers=os.cpu_count() or 1) as ex:
+                list(ex.map(lambda sp: fn(C.byref(sc.rc), out.ctypes.data_as(C.POINTER(C.c_uint8)), sp[0], sp[1], None), spans))
+        else:
+            cpu.render_rows(sc, out, spans, os.cpu_count() or 1)
         for r in rows:
             worst = max(worst, int(np.abs(out[r].astype(np.int16) - frame[r].astype(np.int16)).max()))
             checked += 1
@@ -438,10 +459,16 @@ def run_b200_arm(args, wl):
     launches = int(lt[0])
     # keep the same load running (untimed) until the clock sampler has seen >= 1 s of it; the number of repeats is derived
     # from the reduced time, so every rank runs the same count (the ring needs equal frame sequences on all ranks)
+    soak_events = []
     for _ in range(int(max(0.0, 1.0 - ms / 1e3) / max(ms / 1e3, 1e-6)) + 1):
+        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ea.record(stream)
         rig.sequence(frames)
+        eb.record(stream)
+        soak_events.append((ea, eb))
     rig.barrier()
     clocks.stop()
+    soak_ms = [a.elapsed_time(b) / args.steps for a, b in soak_events]   # this rank's view of the untimed repeats (diagnostic)
     gpu.peer_status()   # raises if any in-kernel or stream wait timed out
 
     # -- the same frames through the per-frame API of round 1 (one launch per frame, frame lanes), for comparison ------
@@ -657,7 +684,7 @@ def run_b200_arm(args, wl):
                 failures.append("verify: NCCL gather frame differs")
         if not args.volume_file:
             rows = [int(r) for r in np.linspace(h // 4, 3 * h // 4, 16)]
-            verify.update(oracle_rows_check(wl, vangles[-1:], alone[-1:], rows, ctx))
+            verify.update(oracle_rows_check(wl, vangles[-1:], alone[-1:], rows, ctx, sampler=args.sampler))
         if verify["sequence_frames_equal"] != VERIFY_K or verify["host_path_frames_equal"] != VERIFY_K or verify.get("max_lsb", 0) != 0:
             failures.append("verify: %r" % verify)
 
@@ -693,6 +720,8 @@ def run_b200_arm(args, wl):
                              "peer": "rank 0 copies the frame gathered in its HBM (vr5_peer_read)",
                              "same": "pipelined: vr5_render_async (kernel + D2H into pinned host memory on the frame's lane) with vr5_set_overlap(%d); the host receives every frame in order, %d frames behind" % (lanes, lanes - 1)}[e2e_gather]},
             "verify": verify,
+            "repeats_ms_per_step": {"n": len(soak_ms), "min": min(soak_ms), "median": float(np.median(soak_ms)), "max": max(soak_ms),
+                                    "note": "the same K-frame sequence repeated back to back after the timed one (untimed load for the clock sampler), rank 0's events"},
             "gpu_launches": launches, "clocks": clocks.summary(),
         }
         if e2e_blocking:
@@ -798,7 +827,7 @@ def c5_record(ctx, args):
         if rig.world == 1 and avail_gib > 28.0:   # CPU rows need the 8-GiB volume on the host: the bytes the kernel sees
             vol = rig.gpu.get_volume((wl["n"],) * 3)
             rows = [int(r) for r in np.linspace(wl["h"] // 4, 3 * wl["h"] // 4, 8)]
-            ver.update(oracle_rows_check(wl, angles[-1:], alone[-1:], rows, ctx, volume=vol))
+            ver.update(oracle_rows_check(wl, angles[-1:], alone[-1:], rows, ctx, volume=vol, sampler=args.sampler))
             del vol
         else:
             ver.update({"oracle_rows": 0, "oracle_note": "CPU rows at 2048^3 are checked at N = 1 with > 28 GiB of free host memory (and in tests/test_gpu_full_size.py)"})
@@ -844,6 +873,7 @@ def main():
     ap.add_argument("--e2e-gather", default="host", choices=["host", "peer"],
                     help="N > 1, end-to-end leg: host = every rank copies its strips into a shared host frame ring; peer = rank 0 copies the gathered frame")
     args = ap.parse_args()
+    claim_stdout()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) != 0:

@@ -184,7 +184,7 @@ int vr5_unpack_strips(vr5_renderer *r, const void *packed_all, uint32_t rows_pad
  * multiple of lanes - and vr5_peer_wait / read / release of a frame are enqueued on that frame's lane. Both conditions are enforced on the device by one-thread wait kernels (bounded: a wait
  * that exceeds the timeout sets a status flag instead of hanging). One process per GPU; never two ranks on one GPU. */
 #define VR5_PEER_HANDLE_BYTES 64
-/* owner: allocate the ring for the current window (vr5_set_window first); slots >= 1 */
+/* owner: allocate the ring for the current window (vr5_set_window first); 1 <= slots <= 32 */
 int vr5_peer_create(vr5_renderer *r, int slots);
 /* owner: IPC handle of the ring (cudaIpcMemHandle_t, 64 bytes) to be sent to the other ranks by any host transport */
 int vr5_peer_export(vr5_renderer *r, void *handle_out64);

@@ -92,7 +92,7 @@ def test_full_size_parity_and_properties(cfg, R, port):
         gpu.close()
 
 
-def test_c5_2048_cubed_properties_and_oracle_rows(R, port):
+def test_c5_2048_cubed_properties_and_oracle_rows(R, port, record_property):
     """synthA 2048^3 (8 GiB, 64-bit voxel offsets: SURVEY H3) at 7680x4320. The 4-GiB window layouts do not apply; the policy
     falls back to the texture path. Oracle rows only where the host has room for the 8 GiB copy."""
     n, w, h = 2048, 7680, 4320
@@ -113,7 +113,12 @@ def test_c5_2048_cubed_properties_and_oracle_rows(R, port):
         lit = int((frames["linear"][..., 3] > 0).sum())
         assert cnt["shaded"] == 0 and cnt["esl_iters"] == 0 and 0.99 * cnt["rays_hit"] <= lit <= cnt["rays_hit"]
         assert cnt["samples"] > 20e9                                         # about 35 G samples per frame
-        if _mem_available_gib() > 40 and os.environ.get("VR5_C5_ORACLE", "1") != "0":
+        # which branch ran is part of the record (junit property + a printed line)
+        oracle_branch = _mem_available_gib() > 40 and os.environ.get("VR5_C5_ORACLE", "1") != "0"
+        record_property("c5_oracle_rows_checked", 6 if oracle_branch else 0)
+        record_property("c5_mem_available_gib", round(_mem_available_gib(), 1))
+        print("C5 ORACLE ROWS: %s (MemAvailable %.1f GiB)" % ("6 rows compared with the restated CPU checker, 0 LSB required" if oracle_branch else "SKIPPED - properties only", _mem_available_gib()))
+        if oracle_branch:
             vol = gpu.get_volume((n, n, n))
             spans = [(0, 2), (h // 2, h // 2 + 2), (h - 2, h)]
             want = _oracle_rows(port, vol, base, view, spans)

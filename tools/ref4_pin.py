@@ -64,7 +64,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--full", action="store_true", help="also C2 (256^3) and C3 (512^3) orbit frames at 1920x1080")
     args = ap.parse_args()
-    import bench  # points fd 1 at stderr; emit() writes the line
+    import bench
+    bench.claim_stdout()  # points fd 1 at stderr; emit() writes the line to the real stdout
     import oracle
     import vr5_loader
     from common import golden_scene

@@ -34,6 +34,7 @@ def main():
     args = ap.parse_args()
 
     import bench
+    bench.claim_stdout()
     import oracle
     import vr5_loader
     from common import parity_report, product_scene

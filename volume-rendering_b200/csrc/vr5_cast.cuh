@@ -31,7 +31,7 @@ constexpr int kWindowGuard = 8;   // guard voxels around the window layout (spec
 // 6 resident CTAs per SM (40 registers) measured best for the window variants (44 registers / 5 CTAs: 0.631 ms per C3 frame,
 // 40 / 6: 0.617, 36 / 7: 0.717 - profiles/r01_sampler_choice.md). 0 = no minimum for the others.
 #ifndef VR5_MIN_CTAS
-#define VR5_MIN_CTAS (SAMPLER >= 2 ? 6 : 0)
+#define VR5_MIN_CTAS (SAMPLER >= 2 ? (SHADE ? 5 : 6) : 0)
 #endif
 
 // Kernel variant ids (template parameter SAMPLER): 0..6 are the public VR5_SAMPLER_* policies. 7..9 are the power-of-two
@@ -119,6 +119,7 @@ struct KArgs {
                              // so the host knows the next base without touching the device (vr5_render.cu, launch)
     uint32_t n_queue;        // padded tile count
     uint32_t tiles_x, tile_rows_local, groups_x, groups_y;
+    uint32_t groups_x_magic;  // ceil(2^32 / groups_x): group / groups_x == umulhi(group, magic) for group < 2^16; 0: divide
     const uint32_t *group_order;  // permutation of the groups (build_group_order) or NULL: row-major
     int cta_fetch;           // 1: a CTA takes 8 queue slots at a time (one barrier per block), 0: every warp takes its own
     Counters *counters;
@@ -288,10 +289,12 @@ __device__ VR5_ESL_INLINE bool skip_leading_empty_space(const KArgs &a, const Es
                                                          Counters &cnt) {
     auto point = [&](float o, float d, float kk) { return FMA ? __fmaf_rn(d, kk, o) : fadd(o, fmul(d, kk)); };
     const float hx = a.hx, hy = a.hy, hz = a.hz;
+#ifndef VR5_NO_ESL_EARLYOUT
     {   // most rays of a dense volume start in a non-empty block: test the first point before setting the loop up
         const uint32_t bx = div_block(a, world_to_voxel(px, hx, a.nx1)), by = div_block(a, world_to_voxel(py, hy, a.ny1)), bz = div_block(a, world_to_voxel(pz, hz, a.nz1));
         if (k <= k_far && ((esl_bits[(bz * 32u + by) & 1023u] >> (bx & 31u)) & 1u) == 0u) return true;
     }
+#endif
 #ifndef VR5_NO_ESL_PREDICT
     if (a.esl == 2 && recip_safe(dx) && recip_safe(dy) && recip_safe(dz)) {
         // (a.esl == 2: the host has checked the view, the step and the block edge, and min_bound == -1: vr5_render.cu fill_args)
@@ -577,8 +580,9 @@ __device__ __forceinline__ void tile_of_slot(const KArgs &a, uint32_t q, uint32_
     uint32_t group = q >> (kGroupLog2X + kGroupLog2Y);
     const uint32_t within = q & ((1u << (kGroupLog2X + kGroupLog2Y)) - 1u);
     if (a.group_order) group = __ldg(a.group_order + group);
-    tx = ((group % a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
-    tyl = ((group / a.groups_x) << kGroupLog2Y) + (within >> kGroupLog2X);
+    const uint32_t gy = a.groups_x_magic ? __umulhi(group, a.groups_x_magic) : group / a.groups_x;   // exact for group < 2^16 (fill_args)
+    tx = ((group - gy * a.groups_x) << kGroupLog2X) + (within & ((1u << kGroupLog2X) - 1u));
+    tyl = (gy << kGroupLog2Y) + (within >> kGroupLog2X);
 }
 
 // ---- persistent warps + atomic tile queue (shared by cast_kernel and tri_kernel) -------------------------------------------
@@ -669,8 +673,10 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
     // the slots this warp (lane 0) / CTA (thread 0) has just finished go to the account; the account is flushed when the next
     // slot belongs to another frame or the queue is exhausted
     auto account = [&](uint32_t finished, uint32_t q_next) {
-        const uint32_t f_next = q_next < n_total ? q_next / a.n_queue : 0xffffffffu;
         uint32_t f_acc = s_acc[warp][0], n_acc = s_acc[warp][1] + (f_acc != 0xffffffffu ? finished : 0u);
+        uint32_t f_next = f_acc;   // same frame unless the slot lies outside it (then: one division per frame)
+        if (q_next >= n_total) f_next = 0xffffffffu;
+        else if (f_acc == 0xffffffffu || q_next - f_acc * a.n_queue >= a.n_queue) f_next = q_next / a.n_queue;
         if (f_acc != 0xffffffffu && f_acc != f_next) { frame_slots_done(a, f_acc, n_acc); n_acc = 0u; }
         s_acc[warp][0] = f_next; s_acc[warp][1] = n_acc;
     };
@@ -697,7 +703,10 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
         if (q >= n_total) break;
         uint32_t f = 0, qi = q;
         if (a.frames) {
-            f = q / a.n_queue; qi = q - f * a.n_queue;   // a block of 8 never straddles frames (n_queue % 32 == 0)
+            // the frame of the slot: almost always the one the warp is in already (one multiply and compare); a division once per frame
+            f = s_view_f[warp];
+            qi = q - f * a.n_queue;
+            if (f == 0xffffffffu || qi >= a.n_queue) { f = q / a.n_queue; qi = q - f * a.n_queue; }   // a block of 8 never straddles frames (n_queue % 32 == 0)
             if (s_view_f[warp] != f) {                   // first tile of this warp in frame f: fetch the frame's record (80 bytes)
                 __syncwarp();
                 if (lane < (int)(sizeof(FrameView) / 4)) reinterpret_cast<uint32_t *>(&s_view[warp])[lane] = __ldg(reinterpret_cast<const uint32_t *>(a.frames + f) + lane);

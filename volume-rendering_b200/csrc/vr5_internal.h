@@ -70,7 +70,7 @@ struct vr5_renderer {
     bool peer_owner = false, peer_ipc_mapped = false;
     int peer_slots = 0;
     size_t peer_frame_stride = 0;
-    uint32_t peer_released_slot[16] = {0};  // owner, host side: releases per slot so far
+    uint32_t peer_released_slot[32] = {0};  // owner, host side: releases per slot so far
     // host frame ring (vr5_hostring.cu): shared host memory, every rank copies its strips there over its own PCIe link
     uint8_t *hr_base = nullptr, *hr_dev = nullptr;  // host address / device alias of the page-locked block
     int hr_slots = 0;

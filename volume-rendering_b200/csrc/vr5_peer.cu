@@ -14,8 +14,8 @@
 
 namespace {
 
-constexpr size_t kHeaderBytes = 8192;          // flag words, one 128-byte line each
-constexpr int kMaxSlots = 16;
+constexpr size_t kHeaderBytes = 16384;          // flag words, one 128-byte line each
+constexpr int kMaxSlots = 32;
 constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;  // a wait that lasts 4 s gives up and raises the status flag
 
 // header layout (uint32 words, one 128-byte line per flag): [32] timed_out, [64 + 64 * slot] arrive[slot] = ranks that
@@ -100,7 +100,7 @@ extern "C" void vr5_peer_close(vr5_renderer *r) {
 
 extern "C" int vr5_peer_create(vr5_renderer *r, int slots) {
     if (!r) return 1;
-    if (slots < 1 || slots > kMaxSlots || !r->frame_bytes) { vr5_fail(r, "vr5_peer_create: need 1..16 slots and vr5_set_window first", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (slots < 1 || slots > kMaxSlots || !r->frame_bytes) { vr5_fail(r, "vr5_peer_create: need 1..32 slots and vr5_set_window first", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     vr5_peer_close(r);
     r->peer_frame_stride = frame_stride(r);

@@ -851,8 +851,11 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     a->tile_rows_local = (uint32_t)r->rank < strips ? (strips - r->rank + r->world - 1) / r->world : 0;
     a->cta_fetch = (!r->tf_opaque && !r->opt.warp_fetch) ? 1 : 0;
     a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
+    if (a->groups_x < 2) a->groups_x = 2;   // (the slots of the padding group lie outside the image and are skipped) keeps the magic below in 32 bits
     a->groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
     a->n_queue = (a->groups_x * a->groups_y) << (kGroupLog2X + kGroupLog2Y);
+    // group / groups_x = umulhi(group, magic), exact for group < 2^16; 0 = more groups than that (beyond 8k x 8k pixels): divide
+    a->groups_x_magic = a->groups_x * a->groups_y < 65536u ? (uint32_t)((0x100000000ull + a->groups_x - 1) / a->groups_x) : 0u;
     a->group_order = nullptr;
     if (const int mode = a->n_queue ? r->opt.queue_order : 0) {
         if (build_group_order(r, a, mode)) return 1;
