@@ -276,7 +276,13 @@ class Rig:
         gpu.set_transfer_fn(self.scene.tf, self.scene.esl_bits)
         gpu.set_window_buffer(w, h)
         gpu.set_overlap(overlap)
-        gpu.set_partition(self.rank, self.world, False)
+        # image-space partition of the device-resident path: cost-balanced contiguous bands (a band reads only its slab of the
+        # volume; with interleaved strips every GPU reads the whole volume for 1/N of the samples) unless the transfer function
+        # can end rays early on its own - then the cost is data-dependent and interleaved strips balance better
+        self.partition = ctx.get("partition", "auto")
+        if self.partition == "auto":
+            self.partition = "strips" if wl["tf"] == "opaque" else "bands"
+        self.apply_partition()
         self.slots = peer_slots(overlap)
         box = [gpu.peer_create(self.slots) if self.rank == 0 else None]
         if self.world > 1:
@@ -285,6 +291,12 @@ class Rig:
                 gpu.peer_open(box[0], self.slots)
             dist.barrier()
         self.seq = 0
+
+    def apply_partition(self):
+        if self.world > 1 and self.partition == "bands":
+            self.gpu.set_partition_bands(self.rank, self.world)
+        else:
+            self.gpu.set_partition(self.rank, self.world, False)
 
     def params(self, i, steps):
         R = self.ctx["R"]
@@ -346,7 +358,7 @@ class Rig:
             for p in frames:
                 out.append(self.gpu.render_volume(p))
         finally:
-            self.gpu.set_partition(self.rank, self.world, False)
+            self.apply_partition()
         return out
 
     def frames_through_ring(self, frames):
@@ -435,7 +447,7 @@ def run_b200_arm(args, wl):
         dist.init_process_group("nccl", device_id=dev)
     stream = torch.cuda.Stream(device=dev)  # a real (non-default) stream shared by the kernels, NCCL and the timing events
     torch.cuda.set_stream(stream)
-    ctx = dict(R=R, dist=dist, rank=rank, world=world, local_rank=local_rank, dev=dev, stream=stream, volume_file=args.volume_file)
+    ctx = dict(R=R, dist=dist, rank=rank, world=world, local_rank=local_rank, dev=dev, stream=stream, volume_file=args.volume_file, partition=args.partition)
     L = R.lib()
     failures = []
 
@@ -520,7 +532,7 @@ def run_b200_arm(args, wl):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         nccl_ms = float(t[0])
         nccl_sha = sha256(frame_dev.cpu().numpy()) if rank == 0 else None   # last frame, for `verify`
-        gpu.set_partition(rank, world, False)
+        rig.apply_partition()
         gpu.set_overlap(lanes)
         del packed, gathered
 
@@ -627,7 +639,7 @@ def run_b200_arm(args, wl):
     rig.barrier()
     if e2e_gather == "host":
         gpu.hostring_detach()
-        gpu.set_partition(rank, world, False)
+        rig.apply_partition()
         ring_mem.close()
         dist.barrier()
         if rank == 0:
@@ -657,8 +669,8 @@ def run_b200_arm(args, wl):
     if rank == 0 and world > 1:    # the whole frame on one GPU, for `ideal = full / N`
         gpu.set_partition(0, 1, False)
         full_ms = float(gpu.render_timed(frames, scratch.data_ptr(), l2_flush=False).mean())
-        gpu.set_partition(rank, world, False)
-    strip_px = (L.vr5_strip_rows(h, rank, world) if world > 1 else h) * w
+        rig.apply_partition()
+    strip_px = (L.vr5_strip_rows(h, rank, world) if world > 1 else h) * w   # (bands: the mean band is as tall as the strips together)
     voxel_bytes = 8.0 if args.sampler.startswith("trilinear") else 1.0   # nearest 1 B per fetch, trilinear 8 B
     alg_bytes_frame = voxel_bytes * (samples_local + shaded_local) / len(frames) + 4.0 * strip_px  # + 4 B per pixel written
     alg_bytes_launch = alg_bytes_frame * len(frames)
@@ -701,7 +713,8 @@ def run_b200_arm(args, wl):
                        "volume": "%d^3" % n, "viewport": "%dx%d" % (w, h), "tf": wl["tf"],
                        "projection": "orthographic", "sampler": args.sampler, "samples_per_frame": samples_total / args.steps,
                        "submission": "one persistent sequence launch per rank for all K frames (vr5_peer_render_sequence), frames consumed in order from a ring of %d device frames" % rig.slots,
-                       "parallelism": ("image-space strips x%d, volume replicated, pixels stored straight into rank 0's frame ring over NVLink peer memory (fused render + gather, hand-shake inside the kernel)" % world) if world > 1 else "single GPU",
+                       "partition": (rig.partition if world > 1 else "none"),
+                       "parallelism": ("image space x%d (%s), volume replicated, pixels stored straight into rank 0's frame ring over NVLink peer memory (fused render + gather, hand-shake inside the kernel)" % (world, "cost-balanced contiguous bands of 4-row strips, re-balanced per frame" if rig.partition == "bands" else "interleaved 4-row strips")) if world > 1 else "single GPU",
                        "l2": "no flush in the timed loop: per frame the kernel reads the %.0f MB volume and writes the %.1f MB frame (L2 is 126 MB); "
                              "the flushed per-kernel time is reported in roofline.single_frame_launch_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
@@ -866,6 +879,8 @@ def main():
     ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2", "trilinear", "trilinear-fma"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap", type=int, default=4, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
+    ap.add_argument("--partition", default="auto", choices=["auto", "bands", "strips"],
+                    help="N > 1, device-resident path: cost-balanced contiguous bands or interleaved 4-row strips (auto: strips for an opaque TF)")
     ap.add_argument("--no-policies", action="store_true", help="skip the policies.trilinear_fma sub-record (N = 1)")
     ap.add_argument("--no-c5", action="store_true", help="skip the c5 sub-record (2048^3 / 7680x4320)")
     ap.add_argument("--c5-frames", type=int, default=8)

@@ -167,6 +167,17 @@ int vr5_memcpy_d2h(vr5_renderer *r, void *host_dst, const void *dev_src, uint64_
  * packed = 0: pixels go to their place in a full width*height frame (other ranks' rows untouched);
  * packed = 1: the rank's strips are stored contiguously, strip j of the rank at row 4*j (vr5_strip_rows rows). */
 int vr5_set_partition(vr5_renderer *r, int rank, int world, int packed);
+/* Contiguous alternative: this renderer renders the 4-row strips first_strip .. first_strip + n_strips - 1 (pixels at their
+ * place in the full frame). A band touches only its slab of the volume - at high GPU counts the interleaved strips make every
+ * GPU read the whole volume for 1/N of the samples - but its cost depends on the view: the caller balances the bands
+ * (vr5_balance_bands). vr5_set_partition returns to interleaved strips. */
+int vr5_set_partition_band(vr5_renderer *r, int first_strip, int n_strips);
+/* Cost-balanced bands, re-balanced for every frame: rank `rank` of `world` renders band `rank` of vr5_balance_bands(frame's
+ * parameters, world). Every rank computes the same bounds from the same parameter bytes. Unpacked (pixels at their place). */
+int vr5_set_partition_bands(vr5_renderer *r, int rank, int world);
+/* first_strip_out[0 .. world]: band i = strips first_strip_out[i] .. first_strip_out[i + 1] - 1 (4-row strips), cut so that the
+ * estimated cost (clipped ray length of a sparse grid of rays + a per-ray constant) is equal per band. Host arithmetic only. */
+int vr5_balance_bands(const vr5_params *p, int world, uint32_t *first_strip_out);
 /* rows of a packed strip buffer for (height, rank, world): 4 * number of strips owned (last strip may be short) */
 uint32_t vr5_strip_rows(uint16_t height, int rank, int world);
 /* On the gathering rank: scatter `world` packed strip buffers (concatenated, each padded to `rows_padded` rows) into

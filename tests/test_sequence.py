@@ -273,8 +273,13 @@ def test_ring_sequence_two_gpus_ipc():
     for p in procs:
         p.start()
     for p in procs:
-        p.join(300)
-    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        p.join(150)
+    codes = [p.exitcode for p in procs]
+    for p in procs:          # a rank that died leaves its partner waiting for flags that never come: do not leave it behind
+        if p.is_alive():
+            p.kill()
+            p.join(10)
+    assert all(c == 0 for c in codes), codes
     assert ret.get(0) is True and ret.get(1) is True
 
 

@@ -98,6 +98,11 @@ def test_volume_broadcast_two_gpus(R, tmp_path):
     for p in procs:
         p.start()
     for p in procs:
-        p.join(300)
-    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        p.join(150)
+    codes = [p.exitcode for p in procs]
+    for p in procs:          # a rank that died leaves its partner waiting for flags that never come: do not leave it behind
+        if p.is_alive():
+            p.kill()
+            p.join(10)
+    assert all(c == 0 for c in codes), codes
     assert ret[0][0] == 8 and ret[1][0] == 8 and ret[0][1] == ret[1][1]   # every rank reproduces the reference's 8 frames from the same bytes

@@ -106,6 +106,9 @@ def lib() -> C.CDLL:
         "vr5_device_free": (None, [vp, vp]),
         "vr5_memcpy_d2h": (C.c_int, [vp, vp, vp, C.c_uint64]),
         "vr5_set_partition": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
+        "vr5_set_partition_band": (C.c_int, [vp, C.c_int, C.c_int]),
+        "vr5_set_partition_bands": (C.c_int, [vp, C.c_int, C.c_int]),
+        "vr5_balance_bands": (C.c_int, [C.POINTER(Params), C.c_int, u32p]),
         "vr5_strip_rows": (C.c_uint32, [C.c_uint16, C.c_int, C.c_int]),
         "vr5_unpack_strips": (C.c_int, [vp, vp, C.c_uint32, C.c_int, vp]),
         "vr5_peer_create": (C.c_int, [vp, C.c_int]),

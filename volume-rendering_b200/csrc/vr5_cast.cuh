@@ -58,9 +58,12 @@ struct FrameView {
     // frame-ring hand-shake (vr5_peer.cu), both optional:
     uint32_t *arrive;          // += 1 (system scope, behind a system fence) by the warp that finishes this rank's last tile of the frame
     const uint32_t *consumed;  // must reach `consumed_target` (acquire, system scope) before any pixel of the frame is stored
-    uint32_t consumed_target, pad;
+    uint32_t consumed_target;
+    // band partition (KArgs::bands): this rank's contiguous band of 4-row strips in THIS frame - the bands are balanced per
+    // view, so they move from frame to frame
+    uint32_t first_strip, n_strips, pad[3];
 };
-static_assert(sizeof(FrameView) == 80, "FrameView layout");
+static_assert(sizeof(FrameView) == 96 && sizeof(FrameView) % 16 == 0, "FrameView layout");
 
 struct RayView { float ox, oy, oz, dx, dy, dz, rx, ry, rz, ux, uy, uz; };
 
@@ -71,6 +74,8 @@ struct KArgs {
     uint32_t *frame_done;    // sequence with hand-shake: queue slots finished per frame (zeroed before the launch)
     uint32_t *timed_out;     // set when a wait for `consumed` gives up (bounded: a missing consumer must not hang the GPU)
     int ring_remote;         // the frames' buffers lie in a peer GPU's memory (system-scope fences before a slot is counted)
+    int bands;               // sequence with per-frame bands: strip offset and count come from the frame's record (rank / tile_rows_local
+                             // hold the single-frame values; tile_rows_local = the tallest band of the sequence sizes the queue)
     // view (ViewBase.h:14-21)
     float ox, oy, oz;        // origin
     float dx, dy, dz;        // direction
@@ -629,22 +634,38 @@ __device__ __forceinline__ void frame_slots_done(const KArgs &a, uint32_t f, uin
 }
 
 // The slot of frame f may be written once the consumer has released the frame that used it before. Frames are released in
-// order, so one shared "highest frame known to be writable" per CTA saves all but the first poll of a frame. Bounded: after
-// 4 s the wait gives up, raises the status flag and the frame is written anyway (a lost consumer must not hang the device).
-__device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, const FrameView *cached, volatile uint32_t *s_ok) {
+// order, so one shared "highest frame known to be writable" per CTA (s_ok) answers all but the first question about a frame.
+// The word to poll may live in a PEER GPU's memory: at most ONE lane per CTA polls it at a time (s_lock), with a pause that
+// backs off to a few microseconds - thousands of warps hammering one remote word over NVLink is how a two-slot ring produced
+// link errors in testing. The others wait on the shared copy. Bounded: after 4 s the wait gives up, raises the ring's status
+// flag and the frame is written anyway (a lost consumer must not hang the device).
+__device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, const FrameView *cached, volatile uint32_t *s_ok, uint32_t *s_lock) {
     if (*s_ok != 0xffffffffu && *s_ok >= f) return;
     const FrameView &fv = *cached;
-    if (fv.consumed) {
-        unsigned long long t0;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        while ((int32_t)(load_acquire_sys_u32(fv.consumed) - fv.consumed_target) < 0) {
+    if (!fv.consumed) { *s_ok = f; return; }   // first use of the slot: nothing to wait for (and so for every earlier frame)
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    unsigned pause = 256;
+    for (;;) {
+        const uint32_t ok = *s_ok;
+        if (ok != 0xffffffffu && ok >= f) return;
+        if (atomicExch(s_lock, 1u) == 0u) {          // this lane polls for the CTA
+            const bool released = (int32_t)(load_acquire_sys_u32(fv.consumed) - fv.consumed_target) >= 0;
             unsigned long long t;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            if (t - t0 > 4000000000ull) { *a.timed_out = 1u; break; }
-            __nanosleep(200);
+            const bool give_up = !released && t - t0 > 4000000000ull;
+            if (give_up) *a.timed_out = 1u;
+            if (released || give_up) {
+                const uint32_t cur = *s_ok;
+                if (cur == 0xffffffffu || cur < f) *s_ok = f;
+            }
+            __threadfence_block();
+            atomicExch(s_lock, 0u);
+            if (released || give_up) return;
         }
+        __nanosleep(pause);
+        if (pause < 4096) pause <<= 1;
     }
-    *s_ok = f;
 }
 
 // ray(view, col, row) -> RGBA8 pixel. COUNT: instrumented pass, nothing is stored.
@@ -653,6 +674,7 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ unsigned s_q;
     __shared__ uint32_t s_ok;          // sequence hand-shake: highest frame whose slot is known to be writable (0xffffffff: none yet)
+    __shared__ uint32_t s_lock;        // 1 while a lane of this CTA polls the consumer's release word
     // finished queue slots are counted per frame, and a warp (CTA with CTA-wide fetch) adds its share to the frame's counter
     // ONCE, when it moves on to another frame or leaves: [w][0] = frame being counted (0xffffffff: none), [w][1] = slots
     __shared__ uint32_t s_acc[kCtaThreads / 32][2];
@@ -665,7 +687,7 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
     }
     const bool shake = !COUNT && a.frames && a.frame_done;
     if (shake) {
-        if (threadIdx.x == 0) s_ok = 0xffffffffu;
+        if (threadIdx.x == 0) { s_ok = 0xffffffffu; s_lock = 0u; }
         if (lane == 0) { s_acc[warp][0] = 0xffffffffu; s_acc[warp][1] = 0u; }
         __syncthreads();
     }
@@ -715,7 +737,7 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
             }
         }
         if (shake) {   // before the march: the frame's slot is almost always free long since
-            if (lane == 0) wait_frame_writable(a, f, &s_view[warp], &s_ok);
+            if (lane == 0) wait_frame_writable(a, f, &s_view[warp], &s_ok, &s_lock);
             __syncwarp();
         }
         uint32_t rgba = 0u;
@@ -723,8 +745,10 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
             uint32_t tx, tyl;
             tile_of_slot(a, qi, tx, tyl);
             const int col = (int)tx * kTileW + (lane & 7);
-            const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane >> 3);
-            if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height)  // ragged edges: lanes outside the image idle
+            const bool fb = a.frames && a.bands;   // the frame's own band (uniform)
+            const uint32_t strip0 = fb ? s_view[warp].first_strip : (uint32_t)a.rank, strips_here = fb ? s_view[warp].n_strips : a.tile_rows_local;
+            const int row = (int)(tyl * a.world + strip0) * kTileH + (lane >> 3);
+            if (tx < a.tiles_x && tyl < strips_here && col < a.width && row < a.height)  // ragged edges: lanes outside the image idle
                 rgba = ray(load_view(a, &s_view[warp]), col, row);
         }
         if (!COUNT) {
@@ -736,8 +760,10 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
             tile_of_slot(a, qi, tx, tyl);
             const int lane2 = threadIdx.x & 31;
             const int col = (int)tx * kTileW + (lane2 & 7);
-            const int row = (int)(tyl * a.world + a.rank) * kTileH + (lane2 >> 3);
-            if (tx < a.tiles_x && tyl < a.tile_rows_local && col < a.width && row < a.height) {
+            const bool fb = a.frames && a.bands;
+            const uint32_t strip0 = fb ? s_view[threadIdx.x >> 5].first_strip : (uint32_t)a.rank, strips_here = fb ? s_view[threadIdx.x >> 5].n_strips : a.tile_rows_local;
+            const int row = (int)(tyl * a.world + strip0) * kTileH + (lane2 >> 3);
+            if (tx < a.tiles_x && tyl < strips_here && col < a.width && row < a.height) {
                 uchar4 *out = a.frames ? s_view[threadIdx.x >> 5].out : a.out;
                 const int out_row = a.packed ? (int)tyl * kTileH + (lane2 >> 3) : row;
                 reinterpret_cast<uint32_t *>(out)[(size_t)out_row * a.width + col] = rgba;

@@ -65,6 +65,8 @@ struct vr5_renderer {
     void *d_counters = nullptr;
     // partition
     int rank = 0, world = 1, packed = 0;
+    int band_first = 0, band_count = -1;   // >= 0: contiguous band of 4-row strips instead of the interleaved ones (vr5_set_partition_band)
+    bool band_auto = false;                // the band is re-balanced for every frame's view (vr5_set_partition_bands)
     // peer ring (vr5_peer.cu): owner allocates, writers map it
     uint8_t *peer_base = nullptr;     // header (flags) + slots frames
     bool peer_owner = false, peer_ipc_mapped = false;

@@ -232,6 +232,13 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     if ((e = cudaMemset(r->d_seq_queue, 0, 128)) != cudaSuccess) return bail("cudaMemset sequence queue", e);
     if ((e = cudaStreamCreateWithFlags(&r->consumer_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate consumer", e);
     if ((e = cudaEventCreateWithFlags(&r->consumer_done, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    {   // sequence records are allocated in stream order: keep freed blocks in the pool instead of returning them to the OS at
+        // every synchronisation (the default release threshold is 0, which made every sequence launch pay a fresh allocation)
+        cudaMemPool_t pool = nullptr;
+        unsigned long long keep = ~0ull;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess && pool) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        cudaGetLastError();
+    }
     // experiment knobs: the environment is read here, once; the launch path only looks at r->opt (vr5_set_option changes it)
     for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX", "VR5_ESL_EXACT"})
         if (const char *v = getenv(name)) vr5_set_option(r, name, v);
@@ -663,6 +670,82 @@ extern "C" int vr5_set_partition(vr5_renderer *r, int rank, int world, int packe
     if (!r) return 1;
     if (world < 1 || rank < 0 || rank >= world) { vr5_fail(r, "vr5_set_partition: need 0 <= rank < world", cudaSuccess, __FILE__, __LINE__); return 1; }
     r->rank = rank; r->world = world; r->packed = packed ? 1 : 0;
+    r->band_first = 0; r->band_count = -1; r->band_auto = false;
+    return 0;
+}
+
+extern "C" int vr5_set_partition_band(vr5_renderer *r, int first_strip, int n_strips) {
+    if (!r) return 1;
+    if (first_strip < 0 || n_strips < 0) { vr5_fail(r, "vr5_set_partition_band: need first_strip >= 0 and n_strips >= 0", cudaSuccess, __FILE__, __LINE__); return 1; }
+    r->packed = 0; r->band_first = first_strip; r->band_count = n_strips; r->band_auto = false;
+    return 0;
+}
+
+// Cost-balanced contiguous bands (north_star: "each GPU renders a load-balanced row strip"). The cost of a 4-row strip is
+// estimated from the clipped length of a sparse grid of its rays (Raycaster::intersect in plain fp32: k_far - k_near in steps,
+// plus a per-ray constant for set-up), interpolated over the strips and cut into `world` equal parts. The estimate sees the
+// geometry only - exact for transfer functions without early termination (the semi-transparent bench TF), a proxy otherwise
+// (an opaque TF is better served by interleaved strips). Pure host arithmetic on the parameters: every rank computes the same
+// bounds from the same bytes. ~400 rays per frame, a few microseconds.
+extern "C" int vr5_balance_bands(const vr5_params *p, int world, uint32_t *first_strip_out) {
+    if (!p || world < 1 || !first_strip_out) return 1;
+    const vr5_view &v = p->view;
+    const int w = v.dims.x, h = v.dims.y, strips = (h + kTileH - 1) / kTileH;
+    if (w < 1 || h < 1) return 1;
+    constexpr int kRows = 32, kCols = 16;
+    const int nr = strips < kRows ? strips : kRows;
+    float cost[kRows];
+    const float inv_step = p->ray_step > 0.0f && std::isfinite(p->ray_step) ? 1.0f / p->ray_step : 1.0f;
+    const float mb[3] = {p->min_bound.x, p->min_bound.y, p->min_bound.z};
+    for (int i = 0; i < nr; i++) {
+        const int strip = (int)(((2 * i + 1) * (int64_t)strips) / (2 * nr));
+        const float cy = (float)(strip * kTileH + kTileH / 2 - h / 2);
+        float sum = 0.0f;
+        for (int j = 0; j < kCols; j++) {
+            const float cx = (float)((2 * j + 1) * w / (2 * kCols) - w / 2);
+            float o[3] = {v.origin.x, v.origin.y, v.origin.z}, d[3] = {v.direction.x, v.direction.y, v.direction.z};
+            const float rr[3] = {v.right_plane.x, v.right_plane.y, v.right_plane.z}, uu[3] = {v.up_plane.x, v.up_plane.y, v.up_plane.z};
+            for (int a = 0; a < 3; a++) { if (v.perspective) d[a] += rr[a] * cx + uu[a] * cy; else o[a] += rr[a] * cx + uu[a] * cy; }
+            float kn = -INFINITY, kf = INFINITY;
+            for (int a = 0; a < 3; a++) {
+                const float e = d[a] == 0.0f ? 0.00001f : d[a];
+                const float k1 = (mb[a] - o[a]) / e, k2 = (-mb[a] - o[a]) / e;
+                kn = fmaxf(kn, fminf(k1, k2)); kf = fminf(kf, fmaxf(k1, k2));
+            }
+            kn = fmaxf(kn, 0.0f);
+            sum += 16.0f + ((kn < kf && kf > 0.0f) ? fminf((kf - kn) * inv_step, 1.0e6f) : 0.0f);   // set-up + samples
+        }
+        cost[i] = std::isfinite(sum) ? sum : 16.0f * kCols;
+    }
+    // cumulative cost over the strips (piecewise-linear between the sampled ones), cut into `world` equal parts
+    std::vector<double> cum((size_t)strips + 1, 0.0);
+    for (int s = 0; s < strips; s++) {
+        const double pos = ((double)s + 0.5) * nr / strips - 0.5;   // position among the samples
+        const int i0 = pos <= 0 ? 0 : pos >= nr - 1 ? nr - 1 : (int)pos, i1 = i0 + 1 < nr ? i0 + 1 : i0;
+        const double t = pos <= 0 ? 0.0 : pos >= nr - 1 ? 0.0 : pos - i0;
+        cum[(size_t)s + 1] = cum[(size_t)s] + (1.0 - t) * cost[i0] + t * cost[i1];
+    }
+    const double total = cum[(size_t)strips];
+    first_strip_out[0] = 0;
+    int s = 0;
+    for (int r = 1; r < world; r++) {
+        const double target = total * r / world;
+        while (s < strips && cum[(size_t)s + 1] <= target) s++;
+        // the cut goes to whichever side of strip s is nearer to the target
+        int cut = (s < strips && target - cum[(size_t)s] > cum[(size_t)s + 1] - target) ? s + 1 : s;
+        const int lo = (int)first_strip_out[r - 1] + (strips >= world ? 1 : 0), hi = strips - (strips >= world ? world - r : 0);   // every band at least one strip when there are enough
+        cut = cut < lo ? lo : cut > hi ? hi : cut;
+        first_strip_out[r] = (uint32_t)cut;
+    }
+    first_strip_out[world] = (uint32_t)strips;
+    return 0;
+}
+
+extern "C" int vr5_set_partition_bands(vr5_renderer *r, int rank, int world) {
+    if (!r) return 1;
+    if (world < 1 || world > 64 || rank < 0 || rank >= world) { vr5_fail(r, "vr5_set_partition_bands: need 0 <= rank < world <= 64", cudaSuccess, __FILE__, __LINE__); return 1; }
+    r->rank = rank; r->world = world; r->packed = 0;
+    r->band_first = 0; r->band_count = 0; r->band_auto = true;
     return 0;
 }
 
@@ -805,6 +888,16 @@ static float frame_reach(const KArgs &a) {
     return reach;
 }
 
+// tile-queue geometry from tiles_x and tile_rows_local: 32x32-pixel groups, slots per frame, the divide-by-multiply constant
+static void set_queue_geometry(KArgs *a) {
+    a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
+    if (a->groups_x < 2) a->groups_x = 2;   // (the slots of the padding group lie outside the image and are skipped) keeps the magic below in 32 bits
+    a->groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
+    a->n_queue = (a->groups_x * a->groups_y) << (kGroupLog2X + kGroupLog2Y);
+    // group / groups_x = umulhi(group, magic), exact for group < 2^16; 0 = more groups than that (beyond 8k x 8k pixels): divide
+    a->groups_x_magic = a->groups_x * a->groups_y < 65536u ? (uint32_t)((0x100000000ull + a->groups_x - 1) / a->groups_x) : 0u;
+}
+
 static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs *a) {
     if (!p) { vr5_fail(r, "vr5_render: NULL params", cudaSuccess, __FILE__, __LINE__); return 1; }
     // the reference's own guard (GPURenderer1.cu:101-102): volume, TF + ESL table, buffer
@@ -846,16 +939,18 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     a->esl_bits = r->d_esl;
     a->out = reinterpret_cast<uchar4 *>(out_dev);
     a->packed = r->packed; a->rank = r->rank; a->world = r->world;
+    if (r->band_auto) {   // cost-balanced bands: this frame's band of this rank
+        uint32_t bounds[65];
+        if (vr5_balance_bands(p, r->world, bounds)) { vr5_fail(r, "vr5_balance_bands failed", cudaSuccess, __FILE__, __LINE__); return 1; }
+        r->band_first = (int)bounds[r->rank]; r->band_count = (int)(bounds[r->rank + 1] - bounds[r->rank]);
+    }
+    if (r->band_count >= 0) { a->rank = r->band_first; a->world = 1; }   // contiguous band: tile row t of the rank = strip band_first + t
     a->tiles_x = (a->width + kTileW - 1) / kTileW;
     const uint32_t strips = (a->height + kTileH - 1) / kTileH;
     a->tile_rows_local = (uint32_t)r->rank < strips ? (strips - r->rank + r->world - 1) / r->world : 0;
+    if (r->band_count >= 0) a->tile_rows_local = (uint32_t)r->band_first < strips ? std::min<uint32_t>((uint32_t)r->band_count, strips - (uint32_t)r->band_first) : 0;
     a->cta_fetch = (!r->tf_opaque && !r->opt.warp_fetch) ? 1 : 0;
-    a->groups_x = (a->tiles_x + (1u << kGroupLog2X) - 1) >> kGroupLog2X;
-    if (a->groups_x < 2) a->groups_x = 2;   // (the slots of the padding group lie outside the image and are skipped) keeps the magic below in 32 bits
-    a->groups_y = (a->tile_rows_local + (1u << kGroupLog2Y) - 1) >> kGroupLog2Y;
-    a->n_queue = (a->groups_x * a->groups_y) << (kGroupLog2X + kGroupLog2Y);
-    // group / groups_x = umulhi(group, magic), exact for group < 2^16; 0 = more groups than that (beyond 8k x 8k pixels): divide
-    a->groups_x_magic = a->groups_x * a->groups_y < 65536u ? (uint32_t)((0x100000000ull + a->groups_x - 1) / a->groups_x) : 0u;
+    set_queue_geometry(a);
     a->group_order = nullptr;
     if (const int mode = a->n_queue ? r->opt.queue_order : 0) {
         if (build_group_order(r, a, mode)) return 1;
@@ -923,8 +1018,11 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
     if ((uint64_t)a.n_queue * (uint64_t)n >= (1ull << 31)) { vr5_fail(r, "vr5_render_sequence: too many tiles for one queue (split the sequence)", cudaSuccess, __FILE__, __LINE__); return 1; }
     std::vector<FrameView> fv((size_t)n);
     bool shake = false;
+    const bool bands = r->band_count >= 0;   // per-frame bands travel in the frame records
+    uint32_t max_rows = a.tile_rows_local;
     for (int i = 0; i < n; i++) {
         const vr5_params &p = frames[i];
+        uint32_t band0 = (uint32_t)a.rank, bandn = a.tile_rows_local;
         if (!targets[i].out_dev) { vr5_fail(r, "vr5_render_sequence: NULL frame buffer", cudaSuccess, __FILE__, __LINE__); return 1; }
         if (i > 0) {
             const vr5_params &q = frames[0];
@@ -936,11 +1034,13 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
             KArgs ai;   // the unclamped variants must hold for every frame: carry the largest reach
             if (fill_args(r, &p, targets[i].out_dev, &ai)) return 1;
             a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
+            band0 = (uint32_t)ai.rank; bandn = ai.tile_rows_local;
+            if (bandn > max_rows) max_rows = bandn;
         }
         const vr5_view &v = p.view;
         fv[i] = FrameView{v.direction.x, v.direction.y, v.direction.z, v.origin.x, v.origin.y, v.origin.z, v.right_plane.x, v.right_plane.y, v.right_plane.z,
                           v.up_plane.x, v.up_plane.y, v.up_plane.z, reinterpret_cast<uchar4 *>(targets[i].out_dev), targets[i].arrive, targets[i].consumed,
-                          targets[i].consumed_target, 0u};
+                          targets[i].consumed_target, band0, bandn, {0u, 0u, 0u}};
         shake |= targets[i].arrive || targets[i].consumed;
     }
     // per-sequence device block [views | done counters], allocated and freed in stream order: sequences may queue up
@@ -950,6 +1050,12 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
     VR5_CUDA(r, cudaMallocAsync(&blk, views_bytes + done_bytes, st));
     VR5_CUDA(r, cudaMemcpyAsync(blk, fv.data(), views_bytes, cudaMemcpyHostToDevice, st));
     if (shake) VR5_CUDA(r, cudaMemsetAsync(blk + views_bytes, 0, done_bytes, st));
+    if (bands) {   // the tallest band of the sequence sizes the per-frame share of the queue
+        a.bands = 1;
+        a.tile_rows_local = max_rows;
+        set_queue_geometry(&a);
+        if ((uint64_t)a.n_queue * (uint64_t)n >= (1ull << 31)) { cudaFreeAsync(blk, st); vr5_fail(r, "vr5_render_sequence: too many tiles for one queue (split the sequence)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    }
     a.frames = reinterpret_cast<const FrameView *>(blk);
     a.n_frames = (uint32_t)n;
     a.frame_done = shake ? reinterpret_cast<uint32_t *>(blk + views_bytes) : nullptr;

@@ -231,6 +231,14 @@ class GPURenderer5:
     def set_partition(self, rank, world, packed):
         self._check(self._L.vr5_set_partition(self._h, rank, world, 1 if packed else 0))
 
+    def set_partition_band(self, first_strip: int, n_strips: int):
+        """Contiguous band of 4-row strips instead of interleaved ones (vr5_set_partition_band)."""
+        self._check(self._L.vr5_set_partition_band(self._h, first_strip, n_strips))
+
+    def set_partition_bands(self, rank: int, world: int):
+        """Cost-balanced contiguous bands, re-balanced per frame (vr5_set_partition_bands)."""
+        self._check(self._L.vr5_set_partition_bands(self._h, rank, world))
+
     def unpack_strips(self, packed_ptr, rows_padded, world, frame_ptr):
         self._check(self._L.vr5_unpack_strips(self._h, packed_ptr, rows_padded, world, frame_ptr))
 
@@ -333,6 +341,14 @@ class GPURenderer5:
 
 
 # ---- volume files (include/vr5.h "volume files"; host side) ---------------------------------------------------------------
+def balance_bands(params: Params, world: int) -> np.ndarray:
+    """Band bounds in 4-row strips for one frame's parameters: band i = strips [b[i], b[i + 1]) (vr5_balance_bands)."""
+    b = np.zeros(world + 1, dtype=np.uint32)
+    if lib().vr5_balance_bands(C.byref(params), world, _u32p(b)) != 0:
+        raise Vr5Error("vr5_balance_bands failed")
+    return b
+
+
 def hostring_bytes(width: int, height: int, slots: int) -> int:
     """Size of a host frame ring (header + slots frames), 0 for an invalid slot count (vr5_hostring_bytes)."""
     return int(lib().vr5_hostring_bytes(width, height, slots))
