@@ -62,7 +62,8 @@ enum { VR5_SAMPLER_LINEAR = 0,  /* x-fastest linear array, LDG.U8 (the reference
        VR5_SAMPLER_HYBRID_WINDOW2 = 6, /* texture : window 1 : 2 */
        /* NOT a parity policy: GPURenderer4's semantics (GPURenderer4.cu:33-97) - trilinear volume fetch, linearly
         * interpolated transfer function - evaluated in software fp32; 8 bytes per sample from an 8-byte-per-cell layout.
-        * Checked bit for bit against the restated CPU checker (trilinear section of the test oracle), SURVEY 8(f) rank 2. */
+        * Bit-equal to the restated CPU checker (trilinear section of the test oracle); within a stated tolerance of the reference's
+        * own GPURenderer4 run in the texture unit (tests/test_trilinear_pin.py), SURVEY 8(f) rank 2. */
        VR5_SAMPLER_TRILINEAR = 16,
        /* The same policy and memory layout with CONTRACTED arithmetic: every a + b*c of the march is one fused multiply-add,
         * as nvcc's default -fmad=true builds the reference's GPU renderers (GPURenderer4.cu:75-86), and the filtering

@@ -314,11 +314,15 @@ void orc_histogram(const uint8_t *data, uint64_t n, float *hist256) {
  * Trilinear sampler policy: a CPU restatement of GPURenderer4's semantics
  * (GPURenderer4.cu:33-97) with the texture unit's arithmetic written out in fp32.
  *
- * Parity status of THIS section: UNPINNED. GPURenderer4 needs legacy texture references (does not compile with
- * CUDA 12) and its filtering runs in the texture unit's 9-bit fixed point, which no CPU code here
- * reproduces. What is restated is the documented filtering formula evaluated in fp32, one rounding per
- * operation, in the order written below; the CUDA trilinear kernel follows the same order and is compared bit
- * for bit against this function, never against the nearest-neighbour parity bar.
+ * Parity status of THIS section: PINNED BY TOLERANCE (round 2). (a) The reference's GPURenderer4.cu, compiled
+ * unmodified over a texture-object shim (oracle/ref_gpu4_texobj.cu), renders the same frames in the B200's texture
+ * unit; the CUDA policies that are bit-equal to this section are held to it under the tolerance stated in
+ * tests/test_trilinear_pin.py (histograms: profiles/r02_ref4_pin.md) - the texture unit filters with 8 fractional
+ * weight bits, which no CPU code here reproduces, so equality is not expected. (b) An independent float64
+ * restatement of the CUDA filtering formulas (tests/test_trilinear_independent.py) agrees with this section to
+ * 0-1 LSB. What is restated is the documented filtering formula evaluated in fp32, one rounding per operation, in
+ * the order written below; the CUDA trilinear kernel follows the same order and is compared bit for bit against
+ * this function, never against the nearest-neighbour parity bar.
  *
  *   volume:  tex3D(volume_texture, (p+1)*0.5) - normalised coordinates, linear filter, clamp, normalised-float
  *            read mode (GPURenderer4.cu:76, :136-141): texel position t = u*n - 0.5, cell i0 = floor(t),
@@ -457,9 +461,8 @@ int orc_render_rows_trilinear(const vr5_raycaster *r, uint8_t *rgba8, int row0, 
 }
 
 /* ---------------------------------------------------------------------------------------------------------
- * Trilinear sampler policy, CONTRACTED arithmetic ("trilinear-fma"). Parity status of THIS section: UNPINNED,
- * for the same reasons as the section above (GPURenderer4 does not build with CUDA 12; the texture unit filters
- * in fixed point).
+ * Trilinear sampler policy, CONTRACTED arithmetic ("trilinear-fma"). Parity status of THIS section: PINNED BY
+ * TOLERANCE like the section above (same two anchors: GPURenderer4 on the GPU, the float64 restatement on the CPU).
  *
  * The reference's GPU renderers are built by nvcc with its default -fmad=true, which contracts every
  * `a + b*c` of their march loops (GPURenderer4.cu:75-86: `pt = origin + direction*k`, `acc = acc + cur*(1 -

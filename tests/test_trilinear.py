@@ -1,10 +1,12 @@
 """Trilinear sampler policy: GPURenderer4's semantics evaluated in software fp32.
 
-The CPU side is oracle_port.c's trilinear section ("parity unpinned": GPURenderer4 cannot be built with CUDA 12 and its
-filtering runs in the texture unit's fixed point). The CUDA policy VR5_SAMPLER_TRILINEAR performs the same fp32 operations
-in the same order and is held to bit equality with that restatement. VR5_SAMPLER_TRILINEAR_FMA is the same policy with the
-contractions nvcc applies to the reference's GPU renderers written out as fused multiply-adds; it is held to bit equality
-with the checker's "trilinear-fma" section and to the stated LSB tolerance against the one-rounding-per-operation policy."""
+The CPU side is oracle_port.c's trilinear sections. Their external anchors are elsewhere: the reference's GPURenderer4 itself,
+compiled unmodified over a texture-object shim and compared under a stated tolerance (tests/test_trilinear_pin.py), and an
+independent float64 restatement of the CUDA filtering formulas (tests/test_trilinear_independent.py). Here the CUDA policy
+VR5_SAMPLER_TRILINEAR, which performs the same fp32 operations in the same order, is held to BIT equality with the restatement;
+VR5_SAMPLER_TRILINEAR_FMA - the same policy with the contractions nvcc applies to the reference's GPU renderers written out as
+fused multiply-adds - to bit equality with the checker's "trilinear-fma" section and to the stated LSB tolerance against the
+one-rounding-per-operation policy."""
 import os
 import subprocess
 

@@ -692,47 +692,60 @@ extern "C" int vr5_balance_bands(const vr5_params *p, int world, uint32_t *first
     const vr5_view &v = p->view;
     const int w = v.dims.x, h = v.dims.y, strips = (h + kTileH - 1) / kTileH;
     if (w < 1 || h < 1) return 1;
-    constexpr int kRows = 32, kCols = 16;
+    constexpr int kRows = 24, kCols = 12;   // 288 rays: the cost profile over the rows is piecewise quadratic, a coarse grid pins it to ~1 %
     const int nr = strips < kRows ? strips : kRows;
-    float cost[kRows];
+    float cost[kRows], pos[kRows];   // cost density per strip at strip position pos[i]
     const float inv_step = p->ray_step > 0.0f && std::isfinite(p->ray_step) ? 1.0f / p->ray_step : 1.0f;
     const float mb[3] = {p->min_bound.x, p->min_bound.y, p->min_bound.z};
+    const float o0[3] = {v.origin.x, v.origin.y, v.origin.z}, d0[3] = {v.direction.x, v.direction.y, v.direction.z};
+    const float rr[3] = {v.right_plane.x, v.right_plane.y, v.right_plane.z}, uu[3] = {v.up_plane.x, v.up_plane.y, v.up_plane.z};
+    float inv0[3];   // orthographic: one direction for all rays
+    for (int a = 0; a < 3; a++) inv0[a] = 1.0f / (d0[a] == 0.0f ? 0.00001f : d0[a]);
+    float cxs[kCols];
+    for (int j = 0; j < kCols; j++) cxs[j] = (float)((2 * j + 1) * w / (2 * kCols) - w / 2);
     for (int i = 0; i < nr; i++) {
-        const int strip = (int)(((2 * i + 1) * (int64_t)strips) / (2 * nr));
-        const float cy = (float)(strip * kTileH + kTileH / 2 - h / 2);
+        pos[i] = ((float)i + 0.5f) * (float)strips / (float)nr;
+        const float cy = (float)((int)pos[i] * kTileH + kTileH / 2 - h / 2);
         float sum = 0.0f;
         for (int j = 0; j < kCols; j++) {
-            const float cx = (float)((2 * j + 1) * w / (2 * kCols) - w / 2);
-            float o[3] = {v.origin.x, v.origin.y, v.origin.z}, d[3] = {v.direction.x, v.direction.y, v.direction.z};
-            const float rr[3] = {v.right_plane.x, v.right_plane.y, v.right_plane.z}, uu[3] = {v.up_plane.x, v.up_plane.y, v.up_plane.z};
-            for (int a = 0; a < 3; a++) { if (v.perspective) d[a] += rr[a] * cx + uu[a] * cy; else o[a] += rr[a] * cx + uu[a] * cy; }
+            const float cx = cxs[j];
             float kn = -INFINITY, kf = INFINITY;
             for (int a = 0; a < 3; a++) {
-                const float e = d[a] == 0.0f ? 0.00001f : d[a];
-                const float k1 = (mb[a] - o[a]) / e, k2 = (-mb[a] - o[a]) / e;
-                kn = fmaxf(kn, fminf(k1, k2)); kf = fminf(kf, fmaxf(k1, k2));
+                const float off = rr[a] * cx + uu[a] * cy;
+                float o = o0[a], inv = inv0[a];
+                if (v.perspective) { const float d = d0[a] + off; inv = 1.0f / (d == 0.0f ? 0.00001f : d); } else o += off;
+                const float k1 = (mb[a] - o) * inv, k2 = (-mb[a] - o) * inv;
+                const float lo = k1 < k2 ? k1 : k2, hi = k1 < k2 ? k2 : k1;   // (ternaries: fminf / fmaxf are libm calls without -ffinite-math-only)
+                kn = lo > kn ? lo : kn; kf = hi < kf ? hi : kf;
             }
-            kn = fmaxf(kn, 0.0f);
-            sum += 16.0f + ((kn < kf && kf > 0.0f) ? fminf((kf - kn) * inv_step, 1.0e6f) : 0.0f);   // set-up + samples
+            kn = kn > 0.0f ? kn : 0.0f;
+            const float len = (kf - kn) * inv_step;
+            sum += 16.0f + ((kn < kf && kf > 0.0f) ? (len < 1.0e6f ? len : 1.0e6f) : 0.0f);   // set-up + samples
         }
-        cost[i] = std::isfinite(sum) ? sum : 16.0f * kCols;
+        cost[i] = std::isfinite(sum) && sum > 0.0f ? sum : 16.0f * kCols;
     }
-    // cumulative cost over the strips (piecewise-linear between the sampled ones), cut into `world` equal parts
-    std::vector<double> cum((size_t)strips + 1, 0.0);
-    for (int s = 0; s < strips; s++) {
-        const double pos = ((double)s + 0.5) * nr / strips - 0.5;   // position among the samples
-        const int i0 = pos <= 0 ? 0 : pos >= nr - 1 ? nr - 1 : (int)pos, i1 = i0 + 1 < nr ? i0 + 1 : i0;
-        const double t = pos <= 0 ? 0.0 : pos >= nr - 1 ? 0.0 : pos - i0;
-        cum[(size_t)s + 1] = cum[(size_t)s] + (1.0 - t) * cost[i0] + t * cost[i1];
+    // The density is constant before the first and after the last sample and linear in between; its integral is cut into `world`
+    // equal parts analytically (a quadratic per segment): no per-strip work. ~4 us per call.
+    double seg_area[kRows + 1], total = 0.0;   // segment k: [x_{k-1}, x_k] with x_{-1} = 0, x_nr = strips
+    for (int k = 0; k <= nr; k++) {
+        const double x0 = k == 0 ? 0.0 : pos[k - 1], x1 = k == nr ? (double)strips : pos[k];
+        const double c0 = cost[k == 0 ? 0 : k - 1], c1 = cost[k == nr ? nr - 1 : k];
+        seg_area[k] = 0.5 * (c0 + c1) * (x1 - x0);
+        total += seg_area[k];
     }
-    const double total = cum[(size_t)strips];
     first_strip_out[0] = 0;
-    int s = 0;
+    int k = 0;
+    double acc = 0.0;
     for (int r = 1; r < world; r++) {
         const double target = total * r / world;
-        while (s < strips && cum[(size_t)s + 1] <= target) s++;
-        // the cut goes to whichever side of strip s is nearer to the target
-        int cut = (s < strips && target - cum[(size_t)s] > cum[(size_t)s + 1] - target) ? s + 1 : s;
+        while (k < nr && acc + seg_area[k] < target) acc += seg_area[k++];
+        const double x0 = k == 0 ? 0.0 : pos[k - 1], x1 = k == nr ? (double)strips : pos[k];
+        const double c0 = cost[k == 0 ? 0 : k - 1], c1 = cost[k == nr ? nr - 1 : k], len = x1 - x0, rem = target - acc;
+        double t;   // c0 t + (c1 - c0) t^2 / (2 len) = rem
+        const double slope = len > 0.0 ? (c1 - c0) / len : 0.0;
+        if (fabs(slope) < 1e-12 * (c0 + c1)) t = c0 > 0.0 ? rem / c0 : 0.0;
+        else t = (-c0 + sqrt(fmax(c0 * c0 + 2.0 * slope * rem, 0.0))) / slope;
+        int cut = (int)floor(x0 + t + 0.5);
         const int lo = (int)first_strip_out[r - 1] + (strips >= world ? 1 : 0), hi = strips - (strips >= world ? world - r : 0);   // every band at least one strip when there are enough
         cut = cut < lo ? lo : cut > hi ? hi : cut;
         first_strip_out[r] = (uint32_t)cut;
