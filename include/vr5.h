@@ -127,6 +127,16 @@ int vr5_sync(vr5_renderer *r);
  * pays one submission. The frames may differ in view.origin / direction / right_plane / up_plane only. Pixels are bit-equal
  * to n_frames vr5_render calls. */
 int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev);
+/* vr5_render_sequence for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same arguments, same
+ * pixels; the per-frame records the kernel reads live in a file-scope device array instead of a block allocated per call, so
+ * the call makes no cudaMalloc / cudaFree / stream-ordered allocation. Limits: n_frames <= VR5_NOALLOC_MAX_FRAMES (more is
+ * refused with an error; the array costs 24 KiB on every GPU that loads the library, until exit); VR5_QUEUE_ORDER must be
+ * "rows". The array is shared by every call on the device and keeps the last call's records (a launch rewrites in full what
+ * it reads, nothing has to start at zero): calls that OVERLAP on the GPU - other handles, other streams - race; calls on one
+ * handle are stream-ordered and safe. Volume, transfer function and window must have been set before (those calls allocate). */
+#define VR5_NOALLOC_MAX_FRAMES 256
+int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev);
 /* Experiment knobs by name (the VR5_* environment variables vr5_create reads ONCE: VR5_QUEUE_ORDER = rows | cols | rings,
  * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_WIN_SX). No effect on the pixels. */
 int vr5_set_option(vr5_renderer *r, const char *name, const char *value);

@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
         "vr5_render_raycaster": (C.c_int, [vp, vp, vp, C.c_int]),
         "vr5_render_async": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),
         "vr5_render_sequence": (C.c_int, [vp, C.POINTER(Params), C.c_int, C.POINTER(vp)]),
+        "vr5_render_sequence_noalloc": (C.c_int, [vp, C.POINTER(Params), C.c_int, C.POINTER(vp)]),
         "vr5_set_option": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
         "vr5_sync": (C.c_int, [vp]),
         "vr5_set_stream": (C.c_int, [vp, vp]),

@@ -1090,6 +1090,85 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
     return rc;
 }
 
+// ---- vr5_render_sequence without any allocation (no counterpart in the reference) ----
+// vr5_render_sequence keeps the per-frame records its kernel reads (views, buffers) in a block it allocates and frees in stream
+// order - an allocation per call, which callers under CUDA graph capture, in tight serving loops or in harnesses that forbid
+// cudaMalloc cannot make. This variant keeps the records in a file-scope device array of VR5_NOALLOC_MAX_FRAMES entries (24 KiB;
+// every GPU that loads the library holds it until exit). ONE array per device: every call overwrites the records of the call
+// before (nothing in it has to start at zero: the records a launch reads are rewritten in full), so two calls that overlap on
+// the GPU - different handles or streams - race; calls on one handle's stream are ordered and safe.
+static __device__ __align__(256) FrameView g_noalloc_frames[VR5_NOALLOC_MAX_FRAMES];
+
+// In host code `g_noalloc_frames` is a host-side stand-in, not a device address: the kernel gets the address that
+// cudaGetSymbolAddress returns, looked up once per device with that device current.
+static FrameView *noalloc_frames_ptr(vr5_renderer *r) {
+    static FrameView *ptrs[64] = {nullptr};
+    if (r->device < 0 || r->device >= 64) { vr5_fail(r, "vr5_render_sequence_noalloc: device ordinal beyond 63", cudaSuccess, __FILE__, __LINE__); return nullptr; }
+    if (!ptrs[r->device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_frames);   // the caller has made r->device current
+        if (e != cudaSuccess || !p) { vr5_fail(r, "cudaGetSymbolAddress(g_noalloc_frames)", e, __FILE__, __LINE__); cudaGetLastError(); return nullptr; }
+        ptrs[r->device] = static_cast<FrameView *>(p);
+    }
+    return ptrs[r->device];
+}
+
+extern "C" int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev) {
+    if (!r) return 1;
+    if (!frames || !outs_dev || n_frames < 1) { vr5_fail(r, "vr5_render_sequence_noalloc: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
+    if (n_frames > VR5_NOALLOC_MAX_FRAMES) {
+        vr5_fail(r, "vr5_render_sequence_noalloc: more than VR5_NOALLOC_MAX_FRAMES (256) frames - split the sequence or use vr5_render_sequence", cudaSuccess, __FILE__, __LINE__);
+        return 1;
+    }
+    if (r->opt.queue_order != 0) {   // the opt-in tile orders build a device table on first use
+        vr5_fail(r, "vr5_render_sequence_noalloc: VR5_QUEUE_ORDER must be rows (the other orders allocate a table)", cudaSuccess, __FILE__, __LINE__);
+        return 1;
+    }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    FrameView *dev_records = noalloc_frames_ptr(r);
+    if (!dev_records) return 1;
+    KArgs a;
+    if (fill_args(r, frames, outs_dev[0], &a)) return 1;
+    static thread_local FrameView fv[VR5_NOALLOC_MAX_FRAMES];   // host staging without the heap
+    const bool bands = r->band_count >= 0;
+    uint32_t max_rows = a.tile_rows_local;
+    for (int i = 0; i < n_frames; i++) {
+        const vr5_params &p = frames[i];
+        uint32_t band0 = (uint32_t)a.rank, bandn = a.tile_rows_local;
+        if (!outs_dev[i]) { vr5_fail(r, "vr5_render_sequence_noalloc: NULL frame buffer", cudaSuccess, __FILE__, __LINE__); return 1; }
+        if (i > 0) {
+            const vr5_params &q = frames[0];
+            const bool same = p.view.dims.x == q.view.dims.x && p.view.dims.y == q.view.dims.y && !p.view.perspective == !q.view.perspective &&
+                              !memcmp(&p.view.light_pos, &q.view.light_pos, sizeof(vr5_f3)) && p.ray_step == q.ray_step && p.ray_threshold == q.ray_threshold &&
+                              !p.esl == !q.esl && p.esl_block_dims == q.esl_block_dims && !memcmp(&p.esl_block_size, &q.esl_block_size, sizeof(vr5_f3)) &&
+                              p.light_kd == q.light_kd && !memcmp(&p.min_bound, &q.min_bound, sizeof(vr5_f3));
+            if (!same) { vr5_fail(r, "vr5_render_sequence_noalloc: frames of a sequence may differ in origin / direction / right_plane / up_plane only", cudaSuccess, __FILE__, __LINE__); return 1; }
+            KArgs ai;
+            if (fill_args(r, &p, outs_dev[i], &ai)) return 1;
+            a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
+            band0 = (uint32_t)ai.rank; bandn = ai.tile_rows_local;
+            if (bandn > max_rows) max_rows = bandn;
+        }
+        const vr5_view &v = p.view;
+        fv[i] = FrameView{v.direction.x, v.direction.y, v.direction.z, v.origin.x, v.origin.y, v.origin.z, v.right_plane.x, v.right_plane.y, v.right_plane.z,
+                          v.up_plane.x, v.up_plane.y, v.up_plane.z, reinterpret_cast<uchar4 *>(outs_dev[i]), nullptr, nullptr, 0u, band0, bandn, {0u, 0u, 0u}};
+    }
+    if (bands) { a.bands = 1; a.tile_rows_local = max_rows; set_queue_geometry(&a); }
+    if ((uint64_t)a.n_queue * (uint64_t)n_frames >= (1ull << 31)) { vr5_fail(r, "vr5_render_sequence_noalloc: too many tiles for one queue (split the sequence)", cudaSuccess, __FILE__, __LINE__); return 1; }
+    cudaStream_t st = r->stream;
+    VR5_CUDA(r, cudaMemcpyAsync(dev_records, fv, (size_t)n_frames * sizeof(FrameView), cudaMemcpyHostToDevice, st));   // pageable source: staged before the call returns
+    a.frames = dev_records;
+    a.n_frames = (uint32_t)n_frames;
+    a.frame_done = nullptr; a.timed_out = nullptr; a.ring_remote = 0;
+    a.queue = r->d_seq_queue;
+    a.queue_base = r->seq_queue_base;
+    r->launch_stream = st;
+    r->last_grid = 0;
+    const int rc = launch_variant(r, a, false);
+    if (r->last_grid) r->seq_queue_base += a.n_queue * (uint32_t)n_frames + r->last_grid * (uint32_t)(kCtaThreads / 32);
+    return rc;
+}
+
 extern "C" int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev) {
     if (!r) return 1;
     if (!frames || !outs_dev || n_frames < 1) { vr5_fail(r, "vr5_render_sequence: bad arguments", cudaSuccess, __FILE__, __LINE__); return 1; }
