@@ -495,15 +495,29 @@ def run_b200_arm(args, wl):
     per_frame_loop(warm)
     rig.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    rig.barrier()
+    launches0 = gpu.launch_count()
     e0.record(stream)
     per_frame_loop(frames)
     e1.record(stream)
+    launches_frames = gpu.launch_count() - launches0
     rig.barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    ms_frames_local = e0.elapsed_time(e1)
+    t = torch.tensor([ms_frames_local], dtype=torch.float64, device=dev)
+    lt = torch.tensor([launches_frames], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_per_frame_api = float(t[0])
+        dist.all_reduce(lt)
+    ms_per_frame_api, launches_frames = float(t[0]), int(lt[0])
     gpu.peer_status()
+    # Which submission is the headline. Both are timed over exactly the same K frames with the same barriers and events, both are
+    # in the line. auto: the sequence launch on one GPU (same rate as frame lanes, one launch instead of ~3 per frame); one launch
+    # per frame over frame lanes on several GPUs - measured faster there (N = 8, C3: 0.079 against 0.102 ms per frame): a rank's
+    # share of a frame is short, and the per-CTA hand-shake inside the sequence kernel costs ~40 us per frame
+    submission = args.submission if args.submission != "auto" else ("sequence" if world == 1 else "frames")
+    ms_sequence, launches_sequence = ms, launches
+    if submission == "frames":
+        ms, launches = ms_per_frame_api, launches_frames
 
     # -- N > 1: the plain-collective baseline (packed strips -> dist.gather over NCCL -> unpack kernel on rank 0) ----------
     nccl_ms = None
@@ -675,8 +689,12 @@ def run_b200_arm(args, wl):
     alg_bytes_frame = voxel_bytes * (samples_local + shaded_local) / len(frames) + 4.0 * strip_px  # + 4 B per pixel written
     alg_bytes_launch = alg_bytes_frame * len(frames)
     peak, peak_src = measured_peak()
-    achieved = alg_bytes_launch / (ms_local * 1e-3) / 1e9
-    traffic, traffic_note = measured_traffic(args.workload, args.sampler, world, len(frames))
+    if submission == "frames":   # the dominant kernel's launch is one frame of this rank
+        alg_bytes_launch, roof_ms, roof_frames = alg_bytes_frame, float(k_ms.mean()), 1
+    else:
+        roof_ms, roof_frames = ms_local, len(frames)
+    achieved = alg_bytes_launch / (roof_ms * 1e-3) / 1e9
+    traffic, traffic_note = measured_traffic(args.workload, args.sampler, world, roof_frames)
 
     # -- verification (untimed): the frames of the timed paths against this GPU alone and against the CPU checker ------------
     vparams, vangles = frames[-VERIFY_K:], frame_angles[-VERIFY_K:]
@@ -708,24 +726,30 @@ def run_b200_arm(args, wl):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": len(warm),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "fps": args.steps / (ms * 1e-3),
-            "ms_per_step_note": "time of the K-frame sequence launch / K: a throughput (all frames of the camera path in one persistent launch), not the latency of one frame; roofline.single_frame_launch_ms is the latter",
+            "ms_per_step_note": ("time of the K-frame sequence launch / K" if submission == "sequence" else "time of K frames submitted one launch each over %d frame lanes / K" % lanes) +
+                                ": a throughput under overlap, not the latency of one frame; roofline.single_frame_launch_ms is the latter",
             "config": {"workload": wl["name"] if not args.volume_file else "%s %s" % (rig.volume_route["file"], "x".join(map(str, rig.volume_route["dims"]))),
                        "volume": "%d^3" % n, "viewport": "%dx%d" % (w, h), "tf": wl["tf"],
                        "projection": "orthographic", "sampler": args.sampler, "samples_per_frame": samples_total / args.steps,
-                       "submission": "one persistent sequence launch per rank for all K frames (vr5_peer_render_sequence), frames consumed in order from a ring of %d device frames" % rig.slots,
+                       "submission": ("one persistent sequence launch per rank for all K frames (vr5_peer_render_sequence), frames consumed in order from a ring of %d device frames" % rig.slots) if submission == "sequence" else
+                                     ("one launch per frame per rank (vr5_peer_render; rank 0: vr5_peer_wait + vr5_peer_release) round-robin over %d frame lanes, ring of %d device frames" % (lanes, rig.slots)),
+                       "submission_choice": "%s (--submission %s)" % (submission, args.submission),
                        "partition": (rig.partition if world > 1 else "none"),
                        "parallelism": ("image space x%d (%s), volume replicated, pixels stored straight into rank 0's frame ring over NVLink peer memory (fused render + gather, hand-shake inside the kernel)" % (world, "cost-balanced contiguous bands of 4-row strips, re-balanced per frame" if rig.partition == "bands" else "interleaved 4-row strips")) if world > 1 else "single GPU",
                        "l2": "no flush in the timed loop: per frame the kernel reads the %.0f MB volume and writes the %.1f MB frame (L2 is 126 MB); "
                              "the flushed per-kernel time is reported in roofline.single_frame_launch_ms_l2_flushed" % (n ** 3 / 1e6, w * h * 4 / 1e6)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
-                         "peak_source": peak_src, "kernel": kernel_name, "launch": "one launch = the K-frame sequence of the timed region (CUDA events on its stream)",
-                         "bytes_per_sample": voxel_bytes, "kernel_ms": ms_local, "frames_per_launch": len(frames), "algorithmic_bytes_per_launch": alg_bytes_launch,
+                         "peak_source": peak_src, "kernel": kernel_name,
+                         "launch": "one launch = the K-frame sequence of the timed region (CUDA events on its stream)" if submission == "sequence" else "one launch = this rank's share of one frame, alone on its stream (per-launch CUDA events, mean over the K frames)",
+                         "bytes_per_sample": voxel_bytes, "kernel_ms": roof_ms, "frames_per_launch": roof_frames, "algorithmic_bytes_per_launch": alg_bytes_launch,
                          "single_frame_launch_ms": float(k_ms.mean()), "single_frame_launch_frac": alg_bytes_frame / (float(k_ms.mean()) * 1e-3) / 1e9 / peak,
                          "single_frame_launch_ms_l2_flushed": float(k_ms_flushed.mean()),
                          "note": ("trilinear policy, contracted arithmetic (GPURenderer4 semantics as nvcc -fmad=true builds them, NOT the CPURenderer parity mode): 8 B per sample" if args.sampler == "trilinear-fma" else
                                   "trilinear policy (GPURenderer4 semantics, NOT the CPURenderer parity mode): 8 B per sample" if args.sampler == "trilinear" else
                                   "parity mode fetches 1 B per sample; the kernel is bound by the fp32 pipe and issue slots, not by HBM (DESIGN.md)")},
-            "per_frame_api": {"ms_per_step": ms_per_frame_api / args.steps, "value": samples_total / (ms_per_frame_api * 1e-3) / 1e9, "frame_overlap_lanes": lanes,
+            "sequence_api": {"ms_per_step": ms_sequence / args.steps, "value": samples_total / (ms_sequence * 1e-3) / 1e9, "gpu_launches": launches_sequence,
+                             "path": "one persistent launch per rank for all K frames, hand-shake inside the kernel (vr5_peer_render_sequence / vr5_peer_consume_sequence)"},
+            "per_frame_api": {"gpu_launches": launches_frames, "ms_per_step": ms_per_frame_api / args.steps, "value": samples_total / (ms_per_frame_api * 1e-3) / 1e9, "frame_overlap_lanes": lanes,
                               "path": "round-1 submission: one launch per frame (vr5_peer_render + wait + release), frames round-robin over %d lanes" % lanes},
             "e2e": {"value": samples_total / e2e_s / 1e9, "unit": UNIT, "fps": args.steps / e2e_s, "h2d_bytes_per_step": C.sizeof(R.Params),
                     "d2h_bytes_per_step": w * h * 4,
@@ -879,6 +903,8 @@ def main():
     ap.add_argument("--sampler", default=os.environ.get("VR5_SAMPLER", "hybridw"), choices=["linear", "brick", "tex3d", "hybrid", "hybridw", "window", "hybridw2", "trilinear", "trilinear-fma"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap", type=int, default=4, help="frame lanes (vr5_set_overlap): 1 = strictly serial frames")
+    ap.add_argument("--submission", default="auto", choices=["auto", "sequence", "frames"],
+                    help="which submission the headline value is taken from (both are always measured): auto = sequence on one GPU, frames on several")
     ap.add_argument("--partition", default="auto", choices=["auto", "bands", "strips"],
                     help="N > 1, device-resident path: cost-balanced contiguous bands or interleaved 4-row strips (auto: strips for an opaque TF)")
     ap.add_argument("--no-policies", action="store_true", help="skip the policies.trilinear_fma sub-record (N = 1)")

@@ -73,6 +73,7 @@ struct KArgs {
     uint32_t n_frames;
     uint32_t *frame_done;    // sequence with hand-shake: queue slots finished per frame (zeroed before the launch)
     uint32_t *timed_out;     // set when a wait for `consumed` gives up (bounded: a missing consumer must not hang the GPU)
+    uint32_t *ring_sync;     // sequence with hand-shake: [0] highest frame of this launch known to be writable (0xffffffff: none), [1] lock of the lane that polls the peer
     int ring_remote;         // the frames' buffers lie in a peer GPU's memory (system-scope fences before a slot is counted)
     int bands;               // sequence with per-frame bands: strip offset and count come from the frame's record (rank / tile_rows_local
                              // hold the single-frame values; tile_rows_local = the tallest band of the sequence sizes the queue)
@@ -634,38 +635,50 @@ __device__ __forceinline__ void frame_slots_done(const KArgs &a, uint32_t f, uin
 }
 
 // The slot of frame f may be written once the consumer has released the frame that used it before. Frames are released in
-// order, so one shared "highest frame known to be writable" per CTA (s_ok) answers all but the first question about a frame.
-// The word to poll may live in a PEER GPU's memory: at most ONE lane per CTA polls it at a time (s_lock), with a pause that
-// backs off to a few microseconds - thousands of warps hammering one remote word over NVLink is how a two-slot ring produced
-// link errors in testing. The others wait on the shared copy. Bounded: after 4 s the wait gives up, raises the ring's status
-// flag and the frame is written anyway (a lost consumer must not hang the device).
-__device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, const FrameView *cached, volatile uint32_t *s_ok, uint32_t *s_lock) {
-    if (*s_ok != 0xffffffffu && *s_ok >= f) return;
-    const FrameView &fv = *cached;
-    if (!fv.consumed) { *s_ok = f; return; }   // first use of the slot: nothing to wait for (and so for every earlier frame)
-    unsigned long long t0;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    unsigned pause = 256;
-    for (;;) {
-        const uint32_t ok = *s_ok;
-        if (ok != 0xffffffffu && ok >= f) return;
-        if (atomicExch(s_lock, 1u) == 0u) {          // this lane polls for the CTA
-            const bool released = (int32_t)(load_acquire_sys_u32(fv.consumed) - fv.consumed_target) >= 0;
+// order, so "highest frame known to be writable" answers every later question about earlier frames. With the hand-shake the
+// queue is read per CTA (the host sets cta_fetch), and the ONE thread that fetches a block for the CTA also asks, between the
+// two barriers of the fetch - the other 255 threads sit in the barrier: no lock, nobody spinning. The release word may live in
+// a PEER GPU's memory, so the question is asked in two steps:
+//   a.ring_sync[0]    <- device-memory copy of the answer for this launch; every CTA reads it (one L2 access per frame)
+//   the peer's word   <- ONE thread per GPU at a time (a.ring_sync[1] is its lock), pause backing off to ~8 us between polls
+// History: every warp polling the peer word gave NVLink errors with a two-slot ring; one lane per warp behind a shared-memory
+// lock with the other lanes spinning cost ~40 us per frame although the slot was free every time. Loads are RELAXED: nothing
+// is read from the slot behind the flag, only written, and a store is issued after the load has returned.
+// Bounded: after 4 s the wait gives up, raises the ring's status flag and the frame is written anyway.
+__device__ __forceinline__ uint32_t load_relaxed_sys_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool frame_known(uint32_t known, uint32_t f) { return known != 0xffffffffu && known >= f; }
+
+// called by one thread of the CTA; *s_ok is the CTA's copy of the answer
+__device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, volatile uint32_t *s_ok) {
+    if (frame_known(*s_ok, f)) return;
+    const FrameView &fv = a.frames[f];
+    const uint32_t *consumed = fv.consumed;
+    if (consumed) {   // (NULL: first use of the slot, nothing to wait for - and so for every earlier frame)
+        const uint32_t target = fv.consumed_target;
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        unsigned pause = 512;
+        for (;;) {
+            if (frame_known(load_relaxed_sys_u32(a.ring_sync), f)) break;                  // the GPU already knows
+            if (atomicCAS(a.ring_sync + 1, 0u, 1u) == 0u) {                                 // this thread asks the peer for the GPU
+                const bool released = (int32_t)(load_relaxed_sys_u32(consumed) - target) >= 0;
+                if (released && !frame_known(load_relaxed_sys_u32(a.ring_sync), f)) atomicExch(a.ring_sync, f);
+                __threadfence();
+                atomicExch(a.ring_sync + 1, 0u);
+                if (released) break;
+            }
             unsigned long long t;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            const bool give_up = !released && t - t0 > 4000000000ull;
-            if (give_up) *a.timed_out = 1u;
-            if (released || give_up) {
-                const uint32_t cur = *s_ok;
-                if (cur == 0xffffffffu || cur < f) *s_ok = f;
-            }
-            __threadfence_block();
-            atomicExch(s_lock, 0u);
-            if (released || give_up) return;
+            if (t - t0 > 4000000000ull) { *a.timed_out = 1u; break; }
+            __nanosleep(pause);
+            if (pause < 8192) pause <<= 1;
         }
-        __nanosleep(pause);
-        if (pause < 4096) pause <<= 1;
     }
+    *s_ok = f;
 }
 
 // ray(view, col, row) -> RGBA8 pixel. COUNT: instrumented pass, nothing is stored.
@@ -674,7 +687,6 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ unsigned s_q;
     __shared__ uint32_t s_ok;          // sequence hand-shake: highest frame whose slot is known to be writable (0xffffffff: none yet)
-    __shared__ uint32_t s_lock;        // 1 while a lane of this CTA polls the consumer's release word
     // finished queue slots are counted per frame, and a warp (CTA with CTA-wide fetch) adds its share to the frame's counter
     // ONCE, when it moves on to another frame or leaves: [w][0] = frame being counted (0xffffffff: none), [w][1] = slots
     __shared__ uint32_t s_acc[kCtaThreads / 32][2];
@@ -687,7 +699,7 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
     }
     const bool shake = !COUNT && a.frames && a.frame_done;
     if (shake) {
-        if (threadIdx.x == 0) { s_ok = 0xffffffffu; s_lock = 0u; }
+        if (threadIdx.x == 0) s_ok = 0xffffffffu;
         if (lane == 0) { s_acc[warp][0] = 0xffffffffu; s_acc[warp][1] = 0u; }
         __syncthreads();
     }
@@ -710,11 +722,25 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
             // barrier per block, so the host only asks for it when rays of neighbouring tiles end together (no opaque TF
             // entry: C4 measured 5 % slower with it). Same counter arithmetic as one slot per warp.
             __syncthreads();
-            if (threadIdx.x == 0) s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
+            if (threadIdx.x == 0) {
+                s_q = atomicAdd(a.queue, (unsigned)(kCtaThreads / 32)) - a.queue_base;
+                if (shake) {
+                    // FIRST count the block just finished (all warps have stored their pixels: they are in the barrier above) -
+                    // a CTA that waited for a slot while holding back its share of an earlier frame would keep that frame from
+                    // ever arriving, and with it the release it is waiting for
+                    account((uint32_t)(kCtaThreads / 32), s_q);
+                    if (s_q < n_total) {        // then: the new block's frame must be writable before anybody marches (almost always: long since)
+                        uint32_t fb = s_ok;     // same frame as the last block unless the slot lies outside it
+                        if (fb == 0xffffffffu || s_q - fb * a.n_queue >= a.n_queue) fb = s_q / a.n_queue;
+                        wait_frame_writable(a, fb, &s_ok);
+                    }
+                }
+            }
             __syncthreads();
-            if (shake && threadIdx.x == 0) account((uint32_t)(kCtaThreads / 32), s_q);   // behind the barrier: the other warps are marching already
             q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
         } else {
+            // (per-warp reads never run with the ring hand-shake: the host forces cta_fetch for it, vr5_sequence_launch - the
+            // in-kernel wait for a released slot exists in the per-CTA fetch only)
             if (shake) __syncwarp();       // the lanes' stores of the previous tile are ordered before lane 0's accounting
             if (lane == 0) {
                 q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
@@ -735,10 +761,6 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
                 if (lane == 0) s_view_f[warp] = f;
                 __syncwarp();
             }
-        }
-        if (shake) {   // before the march: the frame's slot is almost always free long since
-            if (lane == 0) wait_frame_writable(a, f, &s_view[warp], &s_ok, &s_lock);
-            __syncwarp();
         }
         uint32_t rgba = 0u;
         {

@@ -258,7 +258,8 @@ extern "C" int vr5_peer_render_sequence(vr5_renderer *r, const vr5_params *frame
         const uint64_t seq = seq0 + (uint64_t)i;
         const int slot = (int)(seq % slots);
         const uint32_t use = (uint32_t)(seq / slots);
-        t[(size_t)i] = vr5_frame_target{slot_ptr(r, seq), arrive_word(r->peer_base, slot), use ? consumed_word(r->peer_base, slot) : nullptr, use};
+        t[(size_t)i] = vr5_frame_target{slot_ptr(r, seq), arrive_word(r->peer_base, slot), (use && !(r->opt.seq_debug & 1)) ? consumed_word(r->peer_base, slot) : nullptr,
+                                        (r->opt.seq_debug & 4) ? 0u : use};
     }
     return vr5_sequence_launch(r, frames, n, t.data(), timeout_word(r->peer_base), r->peer_owner ? 0 : 1);
 }

@@ -240,7 +240,7 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
         cudaGetLastError();
     }
     // experiment knobs: the environment is read here, once; the launch path only looks at r->opt (vr5_set_option changes it)
-    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX", "VR5_ESL_EXACT"})
+    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX", "VR5_ESL_EXACT", "VR5_SEQ_DEBUG"})
         if (const char *v = getenv(name)) vr5_set_option(r, name, v);
     r->err.clear();
     const char *env = getenv("VR5_SAMPLER");
@@ -820,6 +820,7 @@ extern "C" int vr5_set_option(vr5_renderer *r, const char *name, const char *val
     else if (!strcmp(name, "VR5_TRIF_CTAS")) r->opt.trif_ctas = atoi(value);
     else if (!strcmp(name, "VR5_TRIF_DEPTH")) r->opt.trif_depth = atoi(value);
     else if (!strcmp(name, "VR5_ESL_EXACT")) r->opt.esl_exact = truthy();
+    else if (!strcmp(name, "VR5_SEQ_DEBUG")) r->opt.seq_debug = atoi(value);
     else if (!strcmp(name, "VR5_NO_P2")) r->opt.no_p2 = truthy();        // takes effect at the next layout build
     else if (!strcmp(name, "VR5_WIN_SX")) r->opt.win_sx = (uint32_t)strtoul(value, nullptr, 10);
     else { vr5_fail(r, "vr5_set_option: unknown option", cudaSuccess, __FILE__, __LINE__); return 1; }
@@ -1058,11 +1059,15 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
     }
     // per-sequence device block [views | done counters], allocated and freed in stream order: sequences may queue up
     cudaStream_t st = r->stream;
-    const size_t views_bytes = (size_t)n * sizeof(FrameView), done_bytes = shake ? (size_t)n * sizeof(uint32_t) : 0;
+    // [views | per-frame completion counters | ring_sync: known-writable frame, poller lock]
+    const size_t views_bytes = (size_t)n * sizeof(FrameView), done_bytes = shake ? (size_t)n * sizeof(uint32_t) : 0, sync_bytes = shake ? 2 * sizeof(uint32_t) : 0;
     uint8_t *blk = nullptr;
-    VR5_CUDA(r, cudaMallocAsync(&blk, views_bytes + done_bytes, st));
+    VR5_CUDA(r, cudaMallocAsync(&blk, views_bytes + done_bytes + sync_bytes, st));
     VR5_CUDA(r, cudaMemcpyAsync(blk, fv.data(), views_bytes, cudaMemcpyHostToDevice, st));
-    if (shake) VR5_CUDA(r, cudaMemsetAsync(blk + views_bytes, 0, done_bytes, st));
+    if (shake) {
+        VR5_CUDA(r, cudaMemsetAsync(blk + views_bytes, 0, done_bytes + sync_bytes, st));
+        VR5_CUDA(r, cudaMemsetAsync(blk + views_bytes + done_bytes, 0xff, sizeof(uint32_t), st));   // no frame known yet
+    }
     if (bands) {   // the tallest band of the sequence sizes the per-frame share of the queue
         a.bands = 1;
         a.tile_rows_local = max_rows;
@@ -1078,6 +1083,7 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
     a.frames = reinterpret_cast<const FrameView *>(blk);
     a.n_frames = (uint32_t)n;
     a.frame_done = shake ? reinterpret_cast<uint32_t *>(blk + views_bytes) : nullptr;
+    a.ring_sync = shake ? reinterpret_cast<uint32_t *>(blk + views_bytes + done_bytes) : nullptr;
     a.timed_out = timed_out_dev;
     a.ring_remote = targets_remote ? 1 : 0;
     a.queue = r->d_seq_queue;
