@@ -65,3 +65,50 @@ def test_strip_rows_cover_the_frame(R):
             rows = [part.owned_rows(h, r, world) for r in range(world)]
             assert sorted(np.concatenate(rows).tolist()) == list(range(h))
             assert [len(x) for x in rows] == [part.strip_rows(h, r, world) for r in range(world)]
+
+
+def _band_worker(rank, world, port_no, w, h, ret):
+    """Band partition over gloo: every rank cuts the bands from the frame's parameters ON ITS OWN (no exchange), casts its band
+    with the CPU oracle, and the bands reduced onto rank 0 (element-wise max over zero-initialised frames = disjoint union) give the
+    whole frame - i.e. all ranks computed the same, gap-free, non-overlapping bounds."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port_no))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import oracle
+    import vr5_loader
+    vr5_loader.load()
+    R = vr5_loader.renderer_module()
+    port = oracle.Port()
+    vol = port.synth_a(40, 1)
+    cam = R.camera(w, h, 1, (20, 130, 0), 2.0)
+    sc = port.make_scene(vol, oracle.tf_semi(port.default_base_tf(), 40), oracle.View.from_buffer_copy(bytes(cam)))
+    tf = R.premultiply_tf(R.tf_semi(40))
+    params = R.Scene(None, tf, np.zeros(1024, np.uint32), sc.rc.esl_block_dims, sc.rc.esl_block_size.tup(), sc.rc.ray_step).params(cam)
+    b = R.balance_bands(params, world).astype(int)
+    bounds = [torch.zeros(world + 1, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(bounds, torch.from_numpy(b.astype(np.int64)))
+    same = all(torch.equal(x, bounds[0]) for x in bounds)
+    r0, r1 = int(b[rank]) * 4, min(h, int(b[rank + 1]) * 4)
+    full = np.zeros((h, w, 4), dtype=np.uint8)
+    if r1 > r0:
+        part, _ = port.render(sc, rows=(r0, r1), threads=1)
+        full[r0:r1] = part[r0:r1]
+    t = torch.from_numpy(full)
+    dist.reduce(t, dst=0, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        want, _ = port.render(sc, threads=2)
+        ret["equal"] = bool(np.array_equal(t.numpy(), want)) and same
+        ret["bounds"] = b.tolist()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,w,h", [(2, 96, 70), (3, 64, 57)])
+def test_bands_from_every_rank_make_the_frame(world, w, h):
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    port_no = 31500 + (os.getpid() % 2000) + world
+    mp.spawn(_band_worker, args=(world, port_no, w, h, ret), nprocs=world, join=True)
+    assert ret["equal"], ret.get("bounds")
+    assert ret["bounds"][0] == 0 and ret["bounds"][-1] == (h + 3) // 4
