@@ -578,7 +578,8 @@ def run_b200_arm(args, wl):
         if rank != 0:
             ring_mem = R.ring_memory(ring_name, nbytes, create=False)
         gpu.sync()
-        gpu.set_partition(rank, world, True)     # packed strips for the strided copy
+        if rig.partition != "bands":
+            gpu.set_partition(rank, world, True)     # interleaved strips: packed for the strided copy (bands are copied as one block of rows)
         if rank == 0:
             gpu.hostring_attach(ring_mem, RING_SLOTS, init=True)    # clears the header before anyone else looks at it
         dist.barrier()

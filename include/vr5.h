@@ -244,7 +244,7 @@ void vr5_peer_close(vr5_renderer *r);
  * gathering on one device and copying from there makes that device's PCIe link the limit; here the ring of `slots` frames
  * lives in host memory visible to all ranks (POSIX shared memory between processes; any memory inside one process). Every
  * rank renders its strips packed (vr5_set_partition(..., packed = 1)) and copies them straight to their rows of the
- * frame's slot. Frame seq uses slot seq % slots and lane seq % lanes (slots a multiple of lanes). No device waits for
+ * frame's slot (or, with a band partition - vr5_set_partition_bands - renders its band in place and copies that block of rows). Frame seq uses slot seq % slots and lane seq % lanes (slots a multiple of lanes). No device waits for
  * another one; both hand-shakes (slot released / all strips delivered) are bounded host-side polls of counters in the
  * ring's header (4 s, then an error). */
 uint64_t vr5_hostring_bytes(uint16_t width, uint16_t height, int slots);   /* header + slots frames; slots 1..16 */

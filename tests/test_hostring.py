@@ -21,8 +21,9 @@ def _frame(R, addr, h, w):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("bands", [False, True], ids=["strips", "bands"])
 @pytest.mark.parametrize("lanes,world", [(1, 2), (2, 3)])
-def test_hostring_single_process(lanes, world, R, port, golden, volumes):
+def test_hostring_single_process(lanes, world, bands, R, port, golden, volumes):
     case = next(c for c in golden["cases"] if c["name"] == "synthA64_default_persp")  # 317 x 203: ragged tiles, short last strip
     sc = golden_scene(port, case, volumes(case["volume"]))
     scene, params = product_scene(R, sc)
@@ -40,7 +41,10 @@ def test_hostring_single_process(lanes, world, R, port, golden, volumes):
         for k, g in enumerate(ranks):
             g.set_window_buffer(w, h)
             g.set_scene(scene)
-            g.set_partition(k, world, True)
+            if bands:
+                g.set_partition_bands(k, world)   # this rank's cost-balanced band of every frame, copied as one block of rows
+            else:
+                g.set_partition(k, world, True)
             g.set_overlap(lanes)
             g.hostring_attach(ring, slots, init=(k == 0))
         consumer = ranks[0]

@@ -11,6 +11,7 @@
 //     consumed[slot]    = frames the consumer has released from the slot (plain host store)
 // and both waits are bounded host-side polls (vr5_hostring_render: "the slot's previous frame was released";
 // vr5_hostring_wait: "all ranks delivered").
+#include <algorithm>
 #include <stddef.h>
 #include <stdlib.h>
 #include <string.h>
@@ -132,7 +133,8 @@ extern "C" int vr5_hostring_attach(vr5_renderer *r, void *base, uint64_t bytes, 
 extern "C" int vr5_hostring_render(vr5_renderer *r, const vr5_params *p, uint64_t seq) {
     if (!r) return 1;
     if (!r->hr_base) { vr5_fail(r, "vr5_hostring_render: no ring (vr5_hostring_attach)", cudaSuccess, __FILE__, __LINE__); return 1; }
-    if (!r->packed && r->world > 1) { vr5_fail(r, "vr5_hostring_render: the partition must be packed (vr5_set_partition(..., 1))", cudaSuccess, __FILE__, __LINE__); return 1; }
+    const bool bands = r->band_count >= 0;   // contiguous band (vr5_set_partition_band / _bands): rendered in place, copied as one block of rows
+    if (!r->packed && r->world > 1 && !bands) { vr5_fail(r, "vr5_hostring_render: the partition must be packed strips (vr5_set_partition(..., 1)) or bands", cudaSuccess, __FILE__, __LINE__); return 1; }
     if (r->hr_slots % r->n_lanes) { vr5_fail(r, "vr5_hostring_render: slots must be a multiple of the overlap lanes", cudaSuccess, __FILE__, __LINE__); return 1; }
     VR5_CUDA(r, cudaSetDevice(r->device));
     const uint64_t slots = (uint64_t)r->hr_slots;
@@ -149,7 +151,10 @@ extern "C" int vr5_hostring_render(vr5_renderer *r, const vr5_params *p, uint64_
     const uint32_t rows = r->world > 1 ? vr5_strip_rows(r->height, r->rank, r->world) : r->height;
     const size_t row_bytes = (size_t)r->width * 4u, strip_bytes = row_bytes * 4u;
     uint8_t *dst = slot_ptr(r, seq) + (size_t)r->rank * strip_bytes;
-    if (r->world == 1) {
+    if (bands) {   // vr5_render_into has just cut this frame's band (band_first / band_count)
+        const size_t row0 = (size_t)r->band_first * 4u, row1 = std::min<size_t>(r->height, ((size_t)r->band_first + (size_t)r->band_count) * 4u);
+        if (row1 > row0) VR5_CUDA(r, cudaMemcpyAsync(slot_ptr(r, seq) + row0 * row_bytes, ln.d_frame + row0 * row_bytes, (row1 - row0) * row_bytes, cudaMemcpyDeviceToHost, st));
+    } else if (r->world == 1) {
         VR5_CUDA(r, cudaMemcpyAsync(slot_ptr(r, seq), ln.d_frame, r->frame_bytes, cudaMemcpyDeviceToHost, st));
     } else if (rows) {
         const uint32_t full = rows / 4u, rest = rows % 4u;
