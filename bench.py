@@ -674,7 +674,8 @@ def run_b200_arm(args, wl):
         blk_s = time.perf_counter() - t0
         e2e_blocking = {"value": samples_total / blk_s / 1e9, "unit": UNIT, "fps": args.steps / blk_s, "ms_per_frame": 1e3 * blk_s / args.steps,
                         "path": "vr5_render(handle, params, host pointer, out_is_device = 0): blocking, one frame per call, one lane, pageable host buffer - "
-                                "the call GPURenderer5::render_volume makes (VolR.cpp:110)"}
+                                "the call GPURenderer5::render_volume makes (VolR.cpp:110); inside, the frame is rendered as four cost-balanced bands "
+                                "so that the copy of a band overlaps the kernels of the next ones"}
         gpu.set_overlap(lanes)
 
     # -- a single frame's launch alone (per-launch CUDA events on its stream): what one vr5_render call costs on the device ----

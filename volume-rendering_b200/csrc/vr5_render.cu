@@ -240,7 +240,7 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
         cudaGetLastError();
     }
     // experiment knobs: the environment is read here, once; the launch path only looks at r->opt (vr5_set_option changes it)
-    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX", "VR5_ESL_EXACT", "VR5_SEQ_DEBUG"})
+    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX", "VR5_ESL_EXACT", "VR5_SEQ_DEBUG", "VR5_HOST_SINGLE"})
         if (const char *v = getenv(name)) vr5_set_option(r, name, v);
     r->err.clear();
     const char *env = getenv("VR5_SAMPLER");
@@ -821,6 +821,7 @@ extern "C" int vr5_set_option(vr5_renderer *r, const char *name, const char *val
     else if (!strcmp(name, "VR5_TRIF_DEPTH")) r->opt.trif_depth = atoi(value);
     else if (!strcmp(name, "VR5_ESL_EXACT")) r->opt.esl_exact = truthy();
     else if (!strcmp(name, "VR5_SEQ_DEBUG")) r->opt.seq_debug = atoi(value);
+    else if (!strcmp(name, "VR5_HOST_SINGLE")) r->opt.host_single = truthy();
     else if (!strcmp(name, "VR5_NO_P2")) r->opt.no_p2 = truthy();        // takes effect at the next layout build
     else if (!strcmp(name, "VR5_WIN_SX")) r->opt.win_sx = (uint32_t)strtoul(value, nullptr, 10);
     else { vr5_fail(r, "vr5_set_option: unknown option", cudaSuccess, __FILE__, __LINE__); return 1; }
@@ -1274,11 +1275,59 @@ static int resolve_is_device(vr5_renderer *r, const void *ptr, int hint) {
     return (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged) ? 1 : 0;
 }
 
+// The plugin call as VolR makes it (VolR.cpp:110): blocking, whole frame, HOST buffer, one lane. Done as one launch + one copy
+// the frame's 8 MB cross the bus after the kernel has finished (pageable memory: ~0.5 ms behind a 0.6 ms kernel at 1080p). Here the
+// frame is cut into kHostChunks cost-balanced bands (vr5_balance_bands) rendered by one launch each on the lane streams; the
+// copy of band i runs while bands i + 1 .. are being rendered. Same pixels (each band is the partition path of the same kernel).
+constexpr int kHostChunks = 4;
+static int render_host_chunked(vr5_renderer *r, const vr5_params *p, void *out) {
+    vr5_renderer::Lane &l0 = r->lanes[0];
+    if (!l0.d_frame) { vr5_fail(r, "vr5_render: vr5_set_window not called", cudaSuccess, __FILE__, __LINE__); return 1; }
+    uint32_t bounds[kHostChunks + 1];
+    if (vr5_balance_bands(p, kHostChunks, bounds)) { vr5_fail(r, "vr5_balance_bands failed", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaEventRecord(r->ev_fork, r->stream));   // every chunk is ordered behind what the caller enqueued before
+    const int saved_first = r->band_first, saved_count = r->band_count;
+    const bool saved_auto = r->band_auto;
+    r->band_auto = false;
+    int rc = 0;
+    cudaStream_t st[kHostChunks];
+    for (int c = 0; c < kHostChunks && !rc; c++) {
+        st[c] = c == 0 ? r->stream : r->lanes[c].stream;
+        if (c > 0 && cudaStreamWaitEvent(st[c], r->ev_fork, 0) != cudaSuccess) { rc = 1; break; }
+        r->band_first = (int)bounds[c]; r->band_count = (int)(bounds[c + 1] - bounds[c]);
+        KArgs a;
+        if (fill_args(r, p, l0.d_frame, &a)) { rc = 1; break; }
+        vr5_renderer::Lane &ln = r->lanes[c];
+        a.queue = ln.d_queue;
+        a.queue_base = ln.queue_base;
+        r->launch_stream = st[c];
+        r->last_grid = 0;
+        rc = launch_variant(r, a, false);
+        if (r->last_grid) ln.queue_base += a.n_queue + r->last_grid * (uint32_t)(kCtaThreads / 32);
+    }
+    r->band_first = saved_first; r->band_count = saved_count; r->band_auto = saved_auto;
+    const size_t row_bytes = (size_t)r->width * 4u;
+    for (int c = 0; c < kHostChunks && !rc; c++) {   // all kernels are enqueued: a copy into pageable memory may block the host from here on
+        const size_t row0 = (size_t)bounds[c] * kTileH, row1 = std::min<size_t>(r->height, (size_t)bounds[c + 1] * kTileH);
+        if (row1 > row0 && cudaMemcpyAsync(static_cast<uint8_t *>(out) + row0 * row_bytes, l0.d_frame + row0 * row_bytes, (row1 - row0) * row_bytes,
+                                           cudaMemcpyDeviceToHost, st[c]) != cudaSuccess) rc = 1;
+    }
+    cudaError_t e = cudaSuccess;
+    for (int c = kHostChunks - 1; c >= 0; c--) { const cudaError_t ec = cudaStreamSynchronize(c == 0 ? r->stream : r->lanes[c].stream); if (e == cudaSuccess) e = ec; }
+    if (rc || e != cudaSuccess) { if (e != cudaSuccess || r->err.empty()) vr5_fail(r, "vr5_render (host buffer, chunked)", e, __FILE__, __LINE__); return 1; }
+    return 0;
+}
+
 static int render_impl(vr5_renderer *r, const vr5_params *p, void *out, int out_is_device, bool blocking) {
     if (!r) return 1;
     if (!out) { vr5_fail(r, "vr5_render: NULL buffer", cudaSuccess, __FILE__, __LINE__); return 1; }  // GPURenderer1.cu:101
     VR5_CUDA(r, cudaSetDevice(r->device));
     const int is_dev = resolve_is_device(r, out, out_is_device);
+    if (!is_dev && blocking && r->n_lanes == 1 && r->world == 1 && !r->packed && r->band_count < 0 && !r->opt.host_single && p &&
+        p->view.dims.y >= 8 * kHostChunks * kTileH && p->view.dims.x == r->width && p->view.dims.y == r->height) {
+        r->frame_no++;
+        return render_host_chunked(r, p, out);
+    }
     const int lane = (int)(r->frame_no++ % (uint64_t)r->n_lanes);
     vr5_renderer::Lane &ln = r->lanes[lane];
     if (!is_dev && !ln.d_frame) { vr5_fail(r, "vr5_render: vr5_set_window not called", cudaSuccess, __FILE__, __LINE__); return 1; }
