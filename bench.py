@@ -514,8 +514,7 @@ def run_b200_arm(args, wl):
     # in the line. auto: the sequence launch on one GPU (same rate as frame lanes, one launch instead of ~3 per frame); one launch
     # per frame over frame lanes on several GPUs - measured faster there (N = 8, C3: 0.079 against 0.102 ms per frame): a rank's
     # share of a frame is short, and the per-CTA hand-shake inside the sequence kernel costs ~40 us per frame
-    # (an opaque transfer function wants per-warp queue reads, which the hand-shake of the sequence path excludes: frames there too)
-    submission = args.submission if args.submission != "auto" else ("sequence" if world == 1 and wl["tf"] != "opaque" else "frames")
+    submission = args.submission if args.submission != "auto" else ("sequence" if world == 1 else "frames")
     ms_sequence, launches_sequence = ms, launches
     if submission == "frames":
         ms, launches = ms_per_frame_api, launches_frames

@@ -635,9 +635,9 @@ __device__ __forceinline__ void frame_slots_done(const KArgs &a, uint32_t f, uin
 }
 
 // The slot of frame f may be written once the consumer has released the frame that used it before. Frames are released in
-// order, so "highest frame known to be writable" answers every later question about earlier frames. With the hand-shake the
-// queue is read per CTA (the host sets cta_fetch), and the ONE thread that fetches a block for the CTA also asks, between the
-// two barriers of the fetch - the other 255 threads sit in the barrier: no lock, nobody spinning. The release word may live in
+// order, so "highest frame known to be writable" answers every later question about earlier frames. The thread that fetches
+// from the queue also asks: with per-CTA reads the ONE fetching thread, between the two barriers of the fetch (the other 255
+// threads sit in the barrier: no lock, nobody spinning); with per-warp reads lane 0 of the warp. The release word may live in
 // a PEER GPU's memory, so the question is asked in two steps:
 //   a.ring_sync[0]    <- device-memory copy of the answer for this launch; every CTA reads it (one L2 access per frame)
 //   the peer's word   <- ONE thread per GPU at a time (a.ring_sync[1] is its lock), pause backing off to ~8 us between polls
@@ -652,33 +652,43 @@ __device__ __forceinline__ uint32_t load_relaxed_sys_u32(const uint32_t *p) {
 }
 __device__ __forceinline__ bool frame_known(uint32_t known, uint32_t f) { return known != 0xffffffffu && known >= f; }
 
-// called by one thread of the CTA; *s_ok is the CTA's copy of the answer
+// called by one thread per CTA (per-CTA queue reads) or per warp (per-warp reads); *s_ok is the CTA's cached copy of the answer.
+// Whoever holds the per-GPU lock does not ask about ITS frame but advances the common frontier by one: it polls the release
+// word of the first frame not yet known to be writable (releases come in order: if that one is not released, nothing later
+// is). So every poll works for the waiter that is furthest behind, and a thread whose frame has long been released cannot be
+// starved by threads that poll for later frames - the failure mode of the first versions (a shared-memory lock whose holders
+// each asked about their own frame: the one lane that could have made progress never got the lock, its tile never finished,
+// its frame never arrived, nobody's release ever came - until the 4-s bound).
 __device__ __forceinline__ void wait_frame_writable(const KArgs &a, uint32_t f, volatile uint32_t *s_ok) {
     if (frame_known(*s_ok, f)) return;
-    const FrameView &fv = a.frames[f];
-    const uint32_t *consumed = fv.consumed;
-    if (consumed) {   // (NULL: first use of the slot, nothing to wait for - and so for every earlier frame)
-        const uint32_t target = fv.consumed_target;
-        unsigned long long t0;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        unsigned pause = 512;
-        for (;;) {
-            if (frame_known(load_relaxed_sys_u32(a.ring_sync), f)) break;                  // the GPU already knows
-            if (atomicCAS(a.ring_sync + 1, 0u, 1u) == 0u) {                                 // this thread asks the peer for the GPU
-                const bool released = (int32_t)(load_relaxed_sys_u32(consumed) - target) >= 0;
-                if (released && !frame_known(load_relaxed_sys_u32(a.ring_sync), f)) atomicExch(a.ring_sync, f);
-                __threadfence();
-                atomicExch(a.ring_sync + 1, 0u);
-                if (released) break;
+    unsigned long long t0 = 0;
+    unsigned pause = 256;
+    for (;;) {
+        const uint32_t known = load_relaxed_sys_u32(a.ring_sync);
+        if (frame_known(known, f)) break;
+        bool advanced = false;
+        if (atomicCAS(a.ring_sync + 1, 0u, 1u) == 0u) {                                    // this thread asks for the GPU
+            const uint32_t now = load_relaxed_sys_u32(a.ring_sync);                         // (the frontier may have moved meanwhile)
+            const uint32_t next = now == 0xffffffffu ? 0u : now + 1u;                       // <= f: f is not known yet
+            if (next <= f) {
+                const FrameView &fv = a.frames[next];
+                const uint32_t *consumed = fv.consumed;                                     // NULL: first use of the slot
+                if (!consumed || (int32_t)(load_relaxed_sys_u32(consumed) - fv.consumed_target) >= 0) { atomicExch(a.ring_sync, next); advanced = true; }
+            } else {
+                advanced = true;
             }
-            unsigned long long t;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            if (t - t0 > 4000000000ull) { *a.timed_out = 1u; break; }
-            __nanosleep(pause);
-            if (pause < 8192) pause <<= 1;
+            __threadfence();
+            atomicExch(a.ring_sync + 1, 0u);
         }
+        if (advanced) { pause = 256; continue; }
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t0 == 0) t0 = t;
+        if (t - t0 > 4000000000ull) { *a.timed_out = 1u; break; }
+        __nanosleep(pause);
+        if (pause < 8192) pause <<= 1;
     }
-    *s_ok = f;
+    if (!frame_known(*s_ok, f)) *s_ok = f;
 }
 
 // ray(view, col, row) -> RGBA8 pixel. COUNT: instrumented pass, nothing is stored.
@@ -739,12 +749,16 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
             __syncthreads();
             q = s_q + (threadIdx.x >> 5);  // s_q is a multiple of 8 and n_queue of 32: the exit below is uniform over the CTA
         } else {
-            // (per-warp reads never run with the ring hand-shake: the host forces cta_fetch for it, vr5_sequence_launch - the
-            // in-kernel wait for a released slot exists in the per-CTA fetch only)
             if (shake) __syncwarp();       // the lanes' stores of the previous tile are ordered before lane 0's accounting
             if (lane == 0) {
                 q = atomicAdd(a.queue, 1u) - a.queue_base;  // wrap-safe
-                if (shake) account(1u, q);
+                if (shake) {               // count the finished tile FIRST, then make sure the new tile's frame may be written
+                    account(1u, q);
+                    if (q < n_total) {
+                        uint32_t fw = s_acc[warp][0];   // account() has just stored the new slot's frame there
+                        wait_frame_writable(a, fw, &s_ok);
+                    }
+                }
             }
             q = __shfl_sync(0xffffffffu, q, 0);
         }

@@ -95,7 +95,7 @@ struct vr5_renderer {
         bool tri_clamped = false;   // VR5_TRI_CLAMPED: trilinear march with clamped record indices
         int trif_ctas = 6;          // VR5_TRIF_CTAS: register budget of the contracted trilinear march (CTAs per SM)
         int trif_depth = 2;         // VR5_TRIF_DEPTH: cell requests in flight per ray
-        int seq_debug = 0;          // VR5_SEQ_DEBUG (measurement only, breaks the ring protocol): 1 = sequences do not wait for releases, 4 = they run the wait but every slot counts as released
+        int seq_debug = 0;          // VR5_SEQ_DEBUG (measurement only, breaks the ring protocol): 1 = sequences do not wait for releases, 4 = they run the wait but every slot counts as released, 8 = per-CTA queue reads forced
         bool host_single = false;   // VR5_HOST_SINGLE: the blocking host-buffer call renders the frame with one launch + one copy (no chunks)
         bool esl_exact = false;     // VR5_ESL_EXACT: the leading empty-space loop divides in every iteration (no predicted leaps)
         bool no_p2 = false;         // VR5_NO_P2: never build the power-of-two window

@@ -1075,12 +1075,7 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
         set_queue_geometry(&a);
         if ((uint64_t)a.n_queue * (uint64_t)n >= (1ull << 31)) { cudaFreeAsync(blk, st); vr5_fail(r, "vr5_render_sequence: too many tiles for one queue (split the sequence)", cudaSuccess, __FILE__, __LINE__); return 1; }
     }
-    // With the ring hand-shake the queue is always read per CTA (eight slots = one frame for all eight warps): with per-warp
-    // reads - the warps of a CTA in different frames, each with its own wait - a two-slot ring with a concurrent consumer on
-    // the same GPU stalled until the 4-s bound of the in-kernel wait (tools/dbg_ring.py reproduces it: every run, 7 frames
-    // through 2 slots; 3 frames or 8 slots pass). Not understood yet; the per-CTA protocol passes every test, so it is the
-    // only one used. Costs an opaque transfer function ~5 % of its frame rate on this path.
-    if (shake) a.cta_fetch = 1;
+    if (shake && (r->opt.seq_debug & 8)) a.cta_fetch = 1;   // (measurement knob: per-CTA queue reads whatever the transfer function)
     a.frames = reinterpret_cast<const FrameView *>(blk);
     a.n_frames = (uint32_t)n;
     a.frame_done = shake ? reinterpret_cast<uint32_t *>(blk + views_bytes) : nullptr;
