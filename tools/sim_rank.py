@@ -13,6 +13,7 @@ def main():
     ap.add_argument("--workload", default="c3")
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--sampler", default="hybridw")
+    ap.add_argument("--only", default=None, help="run one configuration only: whole | strips | band-centre | band-edge (for ncu captures)")
     args = ap.parse_args()
     import torch
     import bench, vr5_loader
@@ -45,7 +46,10 @@ def main():
     out = {"workload": wl["name"], "world": args.world, "steps": args.steps}
     strips = (h + 3) // 4
     per = (strips + args.world - 1) // args.world
-    for rank, world in ((0, 1), (0, args.world), (args.world // 2, args.world), ("band-centre", args.world), ("band-edge", args.world)):
+    configs = [(0, 1), (0, args.world), (args.world // 2, args.world), ("band-centre", args.world), ("band-edge", args.world)]
+    if args.only:
+        configs = [c for c in configs if {"whole": c == (0, 1), "strips": c == (0, args.world), "band-centre": c[0] == "band-centre", "band-edge": c[0] == "band-edge"}[args.only]]
+    for rank, world in configs:
         if rank == "band-centre":
             gpu.set_partition_band(per * (args.world // 2), per)
         elif rank == "band-edge":
@@ -64,6 +68,8 @@ def main():
         gpu.set_overlap(1)
         out["rank%s_of_%d" % (rank, world)] = {"sequence_ms_per_frame": seq, "single_frame_launch_ms": single, "four_lanes_ms_per_frame": lan,
                                                "samples_per_frame": samples, "gsamples_sequence": samples / (seq * 1e-3) / 1e9}
+    if "rank0_of_1" not in out:
+        print(json.dumps(out)); gpu.close(); return
     full = out["rank0_of_1"]["sequence_ms_per_frame"]
     for k, v in out.items():
         if isinstance(v, dict) and k != "rank0_of_1":
