@@ -1,11 +1,13 @@
 #!/bin/bash
-# eight-GPU lease: the default bench line at N = 8 (C3 headline + C5 record)
+# eight-GPU lease: the default bench line at N = 8 (C3 headline + C5 record), then 360 steps without C5, then N = 4 on the same box
 mkdir -p gpurun_out; nvidia-smi -L | wc -l
-(NCCL_DEBUG=INFO NCCL_DEBUG_FILE=gpurun_out/r02_n8_nccl_%h_%p.log timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29521 bench.py --gpus 8 --steps 20 --warmup 3 > gpurun_out/r02_n8_bench.json 2> gpurun_out/r02_n8_bench.err; echo "bench rc=$?"); tail -3 gpurun_out/r02_n8_bench.err
+run() { n=$1; name=$2; shift 2; (NCCL_DEBUG=INFO NCCL_DEBUG_FILE=gpurun_out/${name}_nccl_%h_%p.log timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29521 bench.py --gpus $n "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; echo "$name rc=$?"); grep -h "NCCL INFO comm .* nranks\|Init COMPLETE" gpurun_out/${name}_nccl_* 2>/dev/null | head -2 | cut -c1-160; rm -f gpurun_out/${name}_nccl_*; }
+run 8 r02_n8_bench --steps 20 --warmup 3
+run 8 r02_n8_bench_360 --steps 360 --warmup 8 --no-c5
+run 4 r02_n4_bench --steps 20 --warmup 3
 python - <<'PY'
 import json
-d=json.load(open("gpurun_out/r02_n8_bench.json"))
-print("n8 seq ms/frame %.4f"%d["ms_per_step"], "value %.1f"%d["value"], "repeats", d["repeats_ms_per_step"]["median"], "per-frame-api %.4f"%d["per_frame_api"]["ms_per_step"], "nccl %.4f"%d["nccl_gather_baseline"]["ms_per_step"], "e2e fps %.0f"%d["e2e"]["fps"])
-print(" verify", {k:v for k,v in d["verify"].items() if k!="what"}); print(" kernel_vs_ideal", d["kernel_vs_ideal"]); print(" c5", {k:v for k,v in d.get("c5",{}).items() if k in ("ms_per_step","gsamples","verify")})
+for n in ("r02_n8_bench","r02_n8_bench_360","r02_n4_bench"):
+    d=json.load(open("gpurun_out/%s.json"%n))
+    print(n, "headline %.4f (%s) value %.1f seq %.4f repeats %.4f frames %.4f nccl %.4f e2e fps %.0f"%(d["ms_per_step"], d["config"]["submission_choice"], d["value"], d["sequence_api"]["ms_per_step"], d["repeats_ms_per_step"]["median"], d["per_frame_api"]["ms_per_step"], d["nccl_gather_baseline"]["ms_per_step"], d["e2e"]["fps"]), {k:v for k,v in d["verify"].items() if k!="what"}, (d.get("c5") or {}).get("ms_per_step"))
 PY
-rm -f gpurun_out/r02_n8_nccl_*   # keep the merge small
