@@ -69,7 +69,7 @@ __device__ __forceinline__ TriTap tri_request(const TriArgs &t, const TriRegs &g
     const uint32_t bx = tri_axis(px, g.hfx, tap.wx), by = tri_axis(py, g.hfy, tap.wy), bz = tri_axis(pz, g.hfz, tap.wz);
     if (FAST) {
         uint32_t lo;
-        asm("{\n\t.reg .u32 t;\n\tmad.lo.u32 t, %3, %5, %6;\n\tmad.lo.u32 t, %2, %4, t;\n\tshl.b32 %0, %1, 3;\n\tadd.u32 %0, %0, t;\n\t}"
+        asm("{\n\t.reg .u32 t;\n\tshl.b32 t, %1, 3;\n\tadd.u32 t, t, %6;\n\tmad.lo.u32 t, %2, %4, t;\n\tmad.lo.u32 %0, %3, %5, t;\n\t}"
             : "=r"(lo) : "r"(bx), "r"(by), "r"(bz), "r"(g.s1), "r"(g.s2), "r"(g.c0));
         asm("{\n\t.reg .u64 p;\n\tmov.b64 p, {%2, %3};\n\tld.global.nc.v2.u32 {%0, %1}, [p];\n\t}" : "=r"(tap.c.x), "=r"(tap.c.y) : "r"(lo), "r"(g.hi));
     } else {  // record index clamped: the guard records already hold the clamped neighbours, like the checker's index clamp
@@ -157,8 +157,11 @@ __device__ __forceinline__ uint32_t trif_axis(float t, float &w) {
 #endif
 __device__ __forceinline__ void trif_load(const TriArgs &t, const TriRegs &g, uint32_t bx, uint32_t by, uint32_t bz, bool fast, uint2 &c) {
     if (fast) {
+        // (bx * 8 + c0) + by * s1 + bz * s2, every step with ONE kernel-uniform operand (an IMAD takes one uniform register: with
+        // c0 as the addend of the bz * s2 term one of the two had to be moved into a general register per sample) and bz - the
+        // index that arrives last - in the last step
         uint32_t lo;
-        asm("{\n\t.reg .u32 t;\n\tmad.lo.u32 t, %3, %5, %6;\n\tmad.lo.u32 t, %2, %4, t;\n\tshl.b32 %0, %1, 3;\n\tadd.u32 %0, %0, t;\n\t}"
+        asm("{\n\t.reg .u32 t;\n\tshl.b32 t, %1, 3;\n\tadd.u32 t, t, %6;\n\tmad.lo.u32 t, %2, %4, t;\n\tmad.lo.u32 %0, %3, %5, t;\n\t}"
             : "=r"(lo) : "r"(bx), "r"(by), "r"(bz), "r"(g.s1), "r"(g.s2), "r"(g.c0));
         // volatile: the request stays where it is written, ahead of the current sample's arithmetic (ptxas otherwise sinks it below
         // the early-termination branch, to the end of the iteration, and the next iteration starts on its latency)
