@@ -138,7 +138,7 @@ int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames,
 #define VR5_NOALLOC_MAX_FRAMES 256
 int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev);
 /* Experiment knobs by name (the VR5_* environment variables vr5_create reads ONCE: VR5_QUEUE_ORDER = rows | cols | rings,
- * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
+ * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_P2_WIDE = 1 | -1 (64-bit window addressing for every volume | never), VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
  * loop divides in every iteration, VR5_HOST_SINGLE = the blocking host-buffer call uses one launch + one copy). No effect on
  * the pixels. (VR5_SEQ_DEBUG is a measurement knob of the ring hand-shake that BREAKS the protocol: never set it in production.) */
 int vr5_set_option(vr5_renderer *r, const char *name, const char *value);

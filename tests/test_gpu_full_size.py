@@ -93,8 +93,9 @@ def test_full_size_parity_and_properties(cfg, R, port):
 
 
 def test_c5_2048_cubed_properties_and_oracle_rows(R, port, record_property):
-    """synthA 2048^3 (8 GiB, 64-bit voxel offsets: SURVEY H3) at 7680x4320. The 4-GiB window layouts do not apply; the policy
-    falls back to the texture path. Oracle rows only where the host has room for the 8 GiB copy."""
+    """synthA 2048^3 (8 GiB, 64-bit voxel offsets: SURVEY H3) at 7680x4320. The window array is larger than 4 GiB: the default
+    policy runs as kernel variant 10 (64-bit slice term, vr5_cast.cuh kP2Wide), compared with the texture-only fallback
+    (VR5_P2_WIDE=-1) and with the plain linear array. Oracle rows only where the host has room for the 8 GiB copy."""
     n, w, h = 2048, 7680, 4320
     gpu = R.GPURenderer5(0)
     try:
@@ -108,7 +109,13 @@ def test_c5_2048_cubed_properties_and_oracle_rows(R, port, record_property):
         for s in ("hybridw", "linear"):
             gpu.set_sampler(s)
             frames[s] = gpu.render_volume(params)
+            if s == "hybridw":
+                assert gpu.last_variant() == 10, gpu.last_variant()
         assert sha(frames["hybridw"]) == sha(frames["linear"])
+        gpu.set_option("VR5_P2_WIDE", "-1")
+        gpu.set_sampler("hybridw")
+        assert sha(gpu.render_volume(params)) == sha(frames["linear"]) and gpu.last_variant() == 2
+        gpu.set_option("VR5_P2_WIDE", "0")
         cnt = gpu.count(params)
         lit = int((frames["linear"][..., 3] > 0).sum())
         assert cnt["shaded"] == 0 and cnt["esl_iters"] == 0 and 0.99 * cnt["rays_hit"] <= lit <= cnt["rays_hit"]

@@ -52,6 +52,39 @@ def test_golden_frames(name, sampler, golden, port, volumes, R, gpu):
     assert gpu.count(params) == case["counters"]
 
 
+@pytest.mark.parametrize("name", [n for n in _cases() if "96" not in n])
+def test_golden_frames_wide_window(name, golden, port, volumes, R):
+    """Kernel variant 10 (window arrays beyond 4 GiB: 64-bit slice term of the address) forced onto the small power-of-two
+    goldens with VR5_P2_WIDE=1; full size: tests/test_gpu_full_size.py (2048^3)."""
+    case = next(c for c in golden["cases"] if c["name"] == name)
+    vol = volumes(case["volume"])
+    if any(d & (d - 1) for d in vol.shape):
+        pytest.skip("not a power-of-two volume")
+    sc = golden_scene(port, case, vol)
+    scene, params = product_scene(R, sc)
+    g = R.GPURenderer5(0)
+    try:
+        g.set_option("VR5_P2_WIDE", "1")
+        g.set_sampler("hybridw")
+        g.set_window_buffer(case["width"], case["height"])
+        g.set_scene(scene)
+        frame = g.render_volume(params)
+        assert g.last_variant() == 10, g.last_variant()
+        assert sha(frame) == case["frame_sha256"]
+        w, h = case["width"], case["height"]
+        ptrs = [g.device_alloc(w * h * 4) for _ in range(2)]   # ... and as a frame sequence
+        g.render_sequence([params, params], ptrs)
+        g.sync()
+        assert g.last_variant() == 10
+        for p in ptrs:
+            out = np.zeros((h, w, 4), dtype=np.uint8)
+            g.memcpy_d2h(out, p)
+            g.device_free(p)
+            assert sha(out) == case["frame_sha256"]
+    finally:
+        g.close()
+
+
 @pytest.mark.parametrize("sampler", SAMPLERS)
 def test_random_volume_ragged(sampler, port, R, gpu):
     """Non-cubic volume, odd viewport (ragged 8x4 tiles), both projections, product-side scene builders."""

@@ -36,8 +36,10 @@ constexpr int kWindowGuard = 8;   // guard voxels around the window layout (spec
 
 // Kernel variant ids (template parameter SAMPLER): 0..6 are the public VR5_SAMPLER_* policies. 7..9 are the power-of-two
 // specialisations of the three window policies, chosen by the launcher when every volume dimension is a power of two:
-// 7 = texture : window 1 : 1, 8 = window only, 9 = texture : window 1 : 2.
+// 7 = texture : window 1 : 1, 8 = window only, 9 = texture : window 1 : 2. 10 = variant 7 for a window array larger than 4 GiB
+// (2048^3): the slice term of the address is a 32 x 32 -> 64-bit multiply-add, everything else as in 7.
 constexpr int kP2First = 7;
+constexpr int kP2Wide = 10;
 constexpr int kP2Origin = 8;  // voxel index i lives at window / texture coordinate i + kP2Origin on every axis
 __host__ __device__ constexpr bool is_p2(int s) { return s >= kP2First; }
 __host__ __device__ constexpr int p2_mode(int s) { return s - kP2First; }
@@ -431,7 +433,7 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
         unpack2(mul2(dxy, pack2(kq, kq)), mx, my);
         const float nx = fadd(ox, mx), ny = fadd(oy, my), nz = fadd(oz, fmul(dz, kq));
         uint32_t sn;
-        if (FETCH == 5 || FETCH == 6) {
+        if (FETCH == 5 || FETCH == 6 || FETCH == 7) {
             // power-of-two dims: (p + 1) * 2^e is exact, so floor((p + 1) * 2^e) + kP2Origin is read straight out of the
             // mantissa of (p + 1) + (2^(23-e) + kP2Origin * 2^-e) rounded toward zero - no multiply, no F2I.
             f32x2 bxy;
@@ -439,7 +441,11 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
             float bxf, byf;
             unpack2(bxy, bxf, byf);
             const uint32_t bx = __float_as_uint(bxf), by = __float_as_uint(byf), bz = __float_as_uint(__fadd_rz(fadd(nz, 1.0f), win.mz));
-            if (FETCH == 5) {  // window: the biased indices ARE the low address bits (the array is placed so that the biases cancel)
+            if (FETCH == 7) {  // wide window: low word by * sx + bx (no wrap: build_p2), then bz * sxy + {low, hi} mod 2^64
+                asm("{\n\t.reg .u32 t;\n\t.reg .u64 p;\n\tmad.lo.u32 t, %2, %4, %1;\n\tmov.b64 p, {t, %6};\n\tmad.wide.u32 p, %3, %5, p;\n\t"
+                    "ld.global.nc.u8 %0, [p];\n\t}"
+                    : "=r"(sn) : "r"(bx), "r"(by), "r"(bz), "r"(win.sx), "r"(win.sxy), "r"(win.hi));
+            } else if (FETCH == 5) {  // window: the biased indices ARE the low address bits (the array is placed so that the biases cancel)
                 // (a power-of-two row stride would make this a shift-add, but measured 10 % slower: cache-set aliasing)
                 uint32_t lo;
                 asm("{\n\t.reg .u32 t;\n\tmad.lo.u32 t, %2, %4, %1;\n\tmad.lo.u32 %0, %3, %5, t;\n\t}"
@@ -529,6 +535,11 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
             for (;;) {
                 if (VR5_STAGE(5, 0)) break;
                 if (VR5_STAGE(5, 1)) break;
+            }
+        } else if (SAMPLER == kP2Wide) {
+            for (;;) {
+                if (VR5_STAGE(6, 0)) break;
+                if (VR5_STAGE(7, 1)) break;
             }
         } else {
             for (;;) {

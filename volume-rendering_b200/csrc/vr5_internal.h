@@ -99,6 +99,7 @@ struct vr5_renderer {
         bool host_single = false;   // VR5_HOST_SINGLE: the blocking host-buffer call renders the frame with one launch + one copy (no chunks)
         bool esl_exact = false;     // VR5_ESL_EXACT: the leading empty-space loop divides in every iteration (no predicted leaps)
         bool no_p2 = false;         // VR5_NO_P2: never build the power-of-two window
+        int p2_wide = 0;            // VR5_P2_WIDE: 1 = 64-bit window addressing (kP2Wide) also below 4 GiB, -1 = never (texture alone)
         uint32_t win_sx = 0;        // VR5_WIN_SX: row stride of the window layouts (0 = default)
     } opt;
     // bookkeeping

@@ -240,7 +240,7 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
         cudaGetLastError();
     }
     // experiment knobs: the environment is read here, once; the launch path only looks at r->opt (vr5_set_option changes it)
-    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_WIN_SX", "VR5_ESL_EXACT", "VR5_SEQ_DEBUG", "VR5_HOST_SINGLE"})
+    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_P2_WIDE", "VR5_WIN_SX", "VR5_ESL_EXACT", "VR5_SEQ_DEBUG", "VR5_HOST_SINGLE"})
         if (const char *v = getenv(name)) vr5_set_option(r, name, v);
     r->err.clear();
     const char *env = getenv("VR5_SAMPLER");
@@ -449,13 +449,29 @@ static int build_p2(vr5_renderer *r) {
     if (r->opt.win_sx >= r->nx + 2 * G && r->opt.win_sx <= 65536) sx = r->opt.win_sx;  // experiment knob
     const uint32_t rows = r->ny + 2 * G;
     const uint32_t sz = r->nz + 2 * G;
-    const uint64_t size = (uint64_t)sz * rows * sx;
-    if (size >= (1ull << 32)) return 0;
-    const uint32_t sxy = rows * sx;
     // index scale per axis is h = n / 2 = 2^(e-1); magic = 2^(23-(e-1)) + G / h has bit pattern ((150-(e-1)) << 23) + G
     const uint32_t bx = (uint32_t)(150 - (ex - 1)) << 23, by = (uint32_t)(150 - (ey - 1)) << 23, bz = (uint32_t)(150 - (ez - 1)) << 23;
-    const uint32_t a0_lo = bx + by * sx + bz * sxy;  // mod 2^32: where the array must start inside its 4-GiB window
-    if ((uint64_t)a0_lo + size > (1ull << 32)) return 0;
+    uint64_t size = (uint64_t)sz * rows * sx;
+    // An array of 4 GiB or more (2048^3) takes the WIDE variant (kP2Wide): address = bz * sxy + {by * sx + bx, hi} in 64-bit
+    // arithmetic mod 2^64. Its low word by * sx + bx = c_xy + (jy * sx + jx) must not wrap for any in-array (jx, jy); a row
+    // stride a few bytes longer moves c_xy out of the way. VR5_P2_WIDE=1 forces the variant for small volumes (tests).
+    const bool wide = size >= (1ull << 32) || r->opt.p2_wide > 0;
+    if (wide && r->opt.p2_wide < 0) return 0;   // VR5_P2_WIDE=-1: volumes beyond 4 GiB go through the texture alone
+    uint32_t c_xy = 0;
+    if (wide) {
+        bool found = false;
+        for (int tries = 0; tries < 64 && !found; tries++, sx += 2) {
+            c_xy = by * sx + bx;                                   // mod 2^32
+            found = (uint64_t)c_xy + (uint64_t)rows * sx < (1ull << 32) && (uint64_t)rows * sx < (1ull << 32);
+            if (found) break;
+        }
+        if (!found) return 0;
+        size = (uint64_t)sz * rows * sx;
+    }
+    const uint32_t sxy = rows * sx;
+    // mod 2^32: where the array must start inside a 4-GiB window for the biases of the three float patterns to cancel
+    const uint32_t a0_lo = wide ? (uint32_t)((uint64_t)c_xy + (uint64_t)bz * sxy) : bx + by * sx + bz * sxy;
+    if (!wide && (uint64_t)a0_lo + size > (1ull << 32)) return 0;
     CUmemAllocationProp prop;
     memset(&prop, 0, sizeof(prop));
     prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
@@ -464,10 +480,11 @@ static int build_p2(vr5_renderer *r) {
     size_t gran = 0;
     if (v.granularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_MINIMUM) != CUDA_SUCCESS || gran == 0) return 0;
     CUdeviceptr va = 0;
-    const size_t va_size = 1ull << 32;
-    if (v.reserve(&va, va_size, va_size, 0, 0) != CUDA_SUCCESS) return 0;
+    const size_t four_gib = 1ull << 32;
+    const size_t va_size = wide ? (((uint64_t)a0_lo + size + gran + four_gib - 1) / four_gib) * four_gib : four_gib;
+    if (v.reserve(&va, va_size, four_gib, 0, 0) != CUDA_SUCCESS) return 0;
     r->p2_va = va; r->p2_va_size = va_size;
-    if (va & (va_size - 1)) { free_p2(r); return 0; }
+    if (va & (four_gib - 1)) { free_p2(r); return 0; }
     const uint64_t map_lo = a0_lo & ~(uint64_t)(gran - 1);
     uint64_t map_hi = ((uint64_t)a0_lo + size + gran - 1) & ~(uint64_t)(gran - 1);
     if (map_hi > va_size) map_hi = va_size;
@@ -486,6 +503,13 @@ static int build_p2(vr5_renderer *r) {
     r->launches++;
     VR5_CUDA(r, cudaGetLastError());
     r->p2_hi = (uint32_t)((uint64_t)va >> 32);
+    if (wide) {
+        // {low, hi} + bz * sxy must land on a0 + (jz * sxy + jy * sx + jx): hi = high word of a0 - c_xy - Bz * sxy (mod 2^64),
+        // whose low word is zero by the choice of a0_lo
+        const uint64_t k = (uint64_t)(va + a0_lo) - (uint64_t)c_xy - (uint64_t)bz * sxy;
+        if ((uint32_t)k != 0u) { free_p2(r); vr5_fail(r, "p2 wide window: start address is not congruent", cudaSuccess, __FILE__, __LINE__); return 1; }
+        r->p2_hi = (uint32_t)(k >> 32);
+    }
     r->p2_mx = ldexpf(1.0f, 23 - (ex - 1)) + ldexpf((float)G, -(ex - 1));
     r->p2_my = ldexpf(1.0f, 23 - (ey - 1)) + ldexpf((float)G, -(ey - 1));
     r->p2_mz = ldexpf(1.0f, 23 - (ez - 1)) + ldexpf((float)G, -(ez - 1));
@@ -517,7 +541,7 @@ static int build_p2(vr5_renderer *r) {
     td.readMode = cudaReadModeElementType;
     td.normalizedCoords = 0;
     VR5_CUDA(r, cudaCreateTextureObject(&r->tex_p2, &res, &td, nullptr));
-    r->p2_wl = 1; r->p2_sx = sx; r->p2_sxy = sxy;
+    r->p2_wl = wide ? 2 : 1; r->p2_sx = sx; r->p2_sxy = sxy;   // 2: only kP2Wide can address it
     return 0;
 }
 
@@ -823,6 +847,7 @@ extern "C" int vr5_set_option(vr5_renderer *r, const char *name, const char *val
     else if (!strcmp(name, "VR5_SEQ_DEBUG")) r->opt.seq_debug = atoi(value);
     else if (!strcmp(name, "VR5_HOST_SINGLE")) r->opt.host_single = truthy();
     else if (!strcmp(name, "VR5_NO_P2")) r->opt.no_p2 = truthy();        // takes effect at the next layout build
+    else if (!strcmp(name, "VR5_P2_WIDE")) r->opt.p2_wide = strtol(value, nullptr, 10);   // 1 = force, -1 = never; next layout build
     else if (!strcmp(name, "VR5_WIN_SX")) r->opt.win_sx = (uint32_t)strtoul(value, nullptr, 10);
     else { vr5_fail(r, "vr5_set_option: unknown option", cudaSuccess, __FILE__, __LINE__); return 1; }
     return 0;
@@ -1242,9 +1267,9 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
     }
     // power-of-two specialisation of the window policies (the instrumented variant counts through the generic kernels:
     // work counters do not depend on the memory path)
-    if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW && r->p2_wl && !count && cube && window_ok(r, a)) {
+    if (r->sampler >= VR5_SAMPLER_HYBRID_WINDOW && r->p2_wl && (r->p2_wl == 1 || r->sampler == VR5_SAMPLER_HYBRID_WINDOW) && !count && cube && window_ok(r, a)) {
         a.whi = r->p2_hi; a.wmx = r->p2_mx; a.wmy = r->p2_my; a.wmz = r->p2_mz; a.tex_p2 = r->tex_p2; a.wsx = r->p2_sx; a.wsxy = r->p2_sxy;
-        e = launch_p2(r, a, shade, r->sampler - VR5_SAMPLER_HYBRID_WINDOW);
+        e = r->p2_wl == 2 ? launch_p2_id<kP2Wide>(r, a, shade) : launch_p2(r, a, shade, r->sampler - VR5_SAMPLER_HYBRID_WINDOW);
         if (e != cudaSuccess) { vr5_fail(r, "cast_kernel launch", e, __FILE__, __LINE__); return 1; }
         return 0;
     }
