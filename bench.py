@@ -723,7 +723,7 @@ def run_b200_arm(args, wl):
     line = None
     if rank == 0:
         value = samples_total / (ms * 1e-3) / 1e9
-        kernel_name = ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler.startswith("trilinear") else "vr5::cast_kernel<%s, variant %d>" % (args.sampler, gpu.last_variant()))
+        kernel_name = ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler.startswith("trilinear") else "vr5::cast_kernel<%s, variant %d%s>" % (args.sampler, gpu.last_variant(), ", zero-skip" if gpu.last_zero_skip() == 1 else ""))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": len(warm),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -872,7 +872,7 @@ def c5_record(ctx, args):
             ver.update({"oracle_rows": 0, "oracle_note": "CPU rows at 2048^3 are checked at N = 1 with > 28 GiB of free host memory (and in tests/test_gpu_full_size.py)"})
         ver["ok"] = ver["sequence_frames_equal"] == 2 and ver.get("max_lsb", 0) == 0
         rec = {"workload": wl["name"], "n_frames": K, "ms_per_step": ms / K, "fps": K / (ms * 1e-3), "gsamples": s_tot / (ms * 1e-3) / 1e9,
-               "samples_per_frame": s_tot / K, "kernel": "vr5::cast_kernel<%s, variant %d>" % (args.sampler, rig.gpu.last_variant()), "verify": ver}
+               "samples_per_frame": s_tot / K, "kernel": "vr5::cast_kernel<%s, variant %d%s>" % (args.sampler, rig.gpu.last_variant(), ", zero-skip" if rig.gpu.last_zero_skip() == 1 else ""), "verify": ver}
     rig.close()
     return rec
 

@@ -106,6 +106,11 @@ int vr5_get_sampler(const vr5_renderer *r);
  * power-of-two specialisations of 4..6; VR5_SAMPLER_TRILINEAR + 1 is the trilinear march with unclamped 32-bit record
  * addressing, VR5_SAMPLER_TRILINEAR itself the clamped one, likewise VR5_SAMPLER_TRILINEAR_FMA (+ 1)), -1 before any launch. */
 int vr5_last_variant(const vr5_renderer *r);
+/* 1 when the LAST nearest-neighbour launch was a zero-skip build: the transfer function set by vr5_set_transfer_fn starts with
+ * all-zero entries (the reference's own tables do: RaycasterBase.cpp:76-84, alpha 0 below entry 13, colours pre-multiplied) and
+ * samples that classify to them skip the compositing they cannot change (CPURenderer.cpp:29-36: acc + 0 * (1 - acc.a)). Same
+ * pixels; VR5_NO_ZSKIP=1 turns it off. 0 otherwise, -1 for a NULL handle. */
+int vr5_last_zero_skip(const vr5_renderer *r);
 
 /* ---- the hot path ----------------------------------------------------------------------------------------- */
 
@@ -138,7 +143,7 @@ int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames,
 #define VR5_NOALLOC_MAX_FRAMES 256
 int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev);
 /* Experiment knobs by name (the VR5_* environment variables vr5_create reads ONCE: VR5_QUEUE_ORDER = rows | cols | rings,
- * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_P2_WIDE = 1 | -1 (64-bit window addressing for every volume | never), VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
+ * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_NO_ZSKIP, VR5_P2_WIDE = 1 | -1 (64-bit window addressing for every volume | never), VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
  * loop divides in every iteration, VR5_HOST_SINGLE = the blocking host-buffer call uses one launch + one copy). No effect on
  * the pixels. (VR5_SEQ_DEBUG is a measurement knob of the ring hand-shake that BREAKS the protocol: never set it in production.) */
 int vr5_set_option(vr5_renderer *r, const char *name, const char *value);

@@ -86,6 +86,7 @@ def lib() -> C.CDLL:
         "vr5_set_sampler": (C.c_int, [vp, C.c_int]),
         "vr5_get_sampler": (C.c_int, [vp]),
         "vr5_last_variant": (C.c_int, [vp]),
+        "vr5_last_zero_skip": (C.c_int, [vp]),
         "vr5_render": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),
         "vr5_render_raycaster": (C.c_int, [vp, vp, vp, C.c_int]),
         "vr5_render_async": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),

@@ -108,6 +108,7 @@ struct KArgs {
     // march (RaycasterBase.h:24-30)
     float step, threshold;
     float shade_alpha;       // 0.05f when light_kd > 0.01f else +inf: folds the uniform half of CPURenderer.cpp:32
+    uint32_t zero_lim;       // ZS kernels: voxel values below it classify to an all-zero TF entry (host: fill_args); 0 = none
     float kd;
     int esl;
     uint32_t bd_magic;       // ceil(2^32 / esl_block_dims): exact idx / bd for idx < 2^16 via umulhi
@@ -229,7 +230,7 @@ __device__ __forceinline__ uint32_t sample_volume(const KArgs &a, const VolScale
 // Loop-invariant kernel parameters are bounced through shared memory once per CTA and read back with volatile loads:
 // that pins them in general registers for the whole march. Left alone, ptxas re-reads them from the constant bank
 // through the uniform datapath (LDCU) on every iteration - one issue slot each in an issue-bound loop (profiles/).
-struct Pinned { float hx, hy, hz, step, threshold, wmx, wmy, wmz; uint32_t whi, wsx, wsxy; };
+struct Pinned { float hx, hy, hz, step, threshold, wmx, wmy, wmz; uint32_t whi, wsx, wsxy, zero_lim; };
 struct Window { float mx, my, mz; uint32_t hi, sx, sxy; };  // the window constants held in registers
 
 // Packed fp32 pairs (sm_100 add/mul.rn.f32x2 -> SASS FADD2 / FMUL2): two IEEE round-to-nearest results per issue slot,
@@ -375,9 +376,14 @@ __device__ VR5_ESL_INLINE bool skip_leading_empty_space(const KArgs &a, const Es
 }
 
 // ---- one ray (CPURenderer.cpp:11-41). Returns the packed RGBA8 pixel; 0 when the reference leaves it cleared. ----
-template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
+// ZS ("zero skip"): the host has seen that the transfer function starts with all-zero entries (every shipped TF of the reference
+// does: RaycasterBase.cpp:76-84 gives alpha 0 to the first 13 entries and update_transfer_fn pre-multiplies the colours) and
+// that alpha stays inside [0, 1]. A sample that classifies to such an entry leaves the ray exactly as it found it - acc + 0 * (1 -
+// acc.a) == acc for every finite acc, 0 <= 0.05 never shades, acc.a did not exceed the threshold a sample earlier - so its
+// LUT fetch, compositing chain and termination test are skipped: only k += step, the next voxel request and k <= k_far remain.
+template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP, bool ZS = false>
 __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, const VolScale &vs, const Window &win, uint32_t lut_addr, const uint32_t *esl_bits,
-                                             const EslPin *esl_pin, float step, float threshold, int col, int row, Counters &cnt) {
+                                             const EslPin *esl_pin, float step, float threshold, uint32_t zero_lim, int col, int row, Counters &cnt) {
     // View::get_ray (ViewBase.h:23-35)
     const float cx = (float)(col - a.half_w);
     const float cy = (float)(row - a.half_h);
@@ -497,31 +503,34 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
     auto stage = [&](auto fetch_tag, uint32_t &s_cur, float &k_cur, const float k_last, const float &k_next) -> bool {
         const float ka = fadd(k_last, step);
         const uint32_t sn = fetch(fetch_tag, ka);
-        float4 c = lut_fetch(lut_addr, s_cur);  // lut[s] == transfer_fn[s / TF_RATIO]
         if (COUNT) cnt.samples++;
-        if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
-            const float px = fadd(ox, fmul(dx, k_cur)), py = fadd(oy, fmul(dy, k_cur)), pz = fadd(oz, fmul(dz, k_cur));  // the sample's point
-            const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
-            const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
-            const float inv = fdiv(1.0f, __fsqrt_rn(len2));
-            const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
-            const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
-            const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
-            const uint32_t sl = sample_volume<S0, true>(a, vs, qx, qy, qz);  // may leave the cube: always clamped
-            const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s_cur, 255.0f)), a.kd);
-            c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
-            if (COUNT) cnt.shaded++;
+        bool ended = false;
+        if (!(ZS && s_cur < zero_lim)) {  // ZS: a transparent sample has nothing to composite (see ZS above)
+            float4 c = lut_fetch(lut_addr, s_cur);  // lut[s] == transfer_fn[s / TF_RATIO]
+            if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
+                const float px = fadd(ox, fmul(dx, k_cur)), py = fadd(oy, fmul(dy, k_cur)), pz = fadd(oz, fmul(dz, k_cur));  // the sample's point
+                const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
+                const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
+                const float inv = fdiv(1.0f, __fsqrt_rn(len2));
+                const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
+                const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
+                const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
+                const uint32_t sl = sample_volume<S0, true>(a, vs, qx, qy, qz);  // may leave the cube: always clamped
+                const float diffuse = fmul(fsub(fdiv((float)sl, 255.0f), fdiv((float)s_cur, 255.0f)), a.kd);
+                c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
+                if (COUNT) cnt.shaded++;
+            }
+            // acc = acc + c * (1 - acc.a): packed products, scalar accumulation
+            const float t = fsub(1.0f, aa);
+            const f32x2 t2 = pack2(t, t);
+            float qr, qg, qb, qa;
+            unpack2(mul2(pack2(c.x, c.y), t2), qr, qg);
+            unpack2(mul2(pack2(c.z, c.w), t2), qb, qa);
+            ar = fadd(ar, qr); ag = fadd(ag, qg); ab = fadd(ab, qb); aa = fadd(aa, qa);
+            ended = aa > threshold;                    // early ray termination, strict >
         }
-        // acc = acc + c * (1 - acc.a): packed products, scalar accumulation
-        const float t = fsub(1.0f, aa);
-        const f32x2 t2 = pack2(t, t);
-        float qr, qg, qb, qa;
-        unpack2(mul2(pack2(c.x, c.y), t2), qr, qg);
-        unpack2(mul2(pack2(c.z, c.w), t2), qb, qa);
-        ar = fadd(ar, qr); ag = fadd(ag, qg); ab = fadd(ab, qb); aa = fadd(aa, qa);
         s_cur = sn; k_cur = ka;
-        if (aa > threshold) return true;               // early ray termination, strict >
-        return !((kPrefetch > 1 ? k_next : ka) <= k_far);  // while (k <= k_far) for the NEXT sample
+        return ended || !((kPrefetch > 1 ? k_next : ka) <= k_far);  // while (k <= k_far) for the NEXT sample
     };
     // stage u of the unrolled loop works on slot u % kPrefetch; its fetch path follows the sampler's pattern
 #define VR5_STAGE(TAG, U) stage(FetchTag<TAG>(), ss[(U) % kPrefetch], ks[(U) % kPrefetch], ks[((U) + kPrefetch - 1) % kPrefetch], ks[((U) + 1) % kPrefetch])
@@ -822,7 +831,7 @@ __device__ __forceinline__ void run_tile_queue(const KArgs &a, RayFn &&ray) {
 // ---- the kernel ---------------------------------------------------------------------------------------------------------
 // SHADE=false is chosen by the host when no sample can take the shading path (light_kd <= 0.01 or no TF entry with
 // alpha > 0.05), CLAMP=false when the sampler is the padded 3-D texture and min_bound == (-1,-1,-1).
-template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP>
+template <int SAMPLER, bool COUNT, bool SHADE, bool CLAMP, bool ZS = false>
 __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const __grid_constant__ KArgs a) {
     __shared__ float4 s_lut[256];
     __shared__ uint32_t s_esl[1024];
@@ -831,19 +840,20 @@ __global__ void __launch_bounds__(kCtaThreads, VR5_MIN_CTAS) cast_kernel(const _
     for (int i = threadIdx.x; i < 256; i += kCtaThreads) s_lut[i] = a.tf[i >> 1];
     for (int i = threadIdx.x; i < 1024; i += kCtaThreads) s_esl[i] = a.esl_bits[i];
     if (threadIdx.x == 32) s_esl_pin = make_esl_pin(a);
-    if (threadIdx.x == 0) s_pinned = Pinned{a.hx, a.hy, a.hz, a.step, a.threshold, a.wmx, a.wmy, a.wmz, a.whi, a.wsx, a.wsxy};
+    if (threadIdx.x == 0) s_pinned = Pinned{a.hx, a.hy, a.hz, a.step, a.threshold, a.wmx, a.wmy, a.wmz, a.whi, a.wsx, a.wsxy, a.zero_lim};
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
     const volatile Pinned *pinned = &s_pinned;
     const VolScale vs = {pinned->hx, pinned->hy, pinned->hz};
     const float step = pinned->step, threshold = pinned->threshold;
+    const uint32_t zero_lim = ZS ? pinned->zero_lim : 0u;
     Window win = {0.0f, 0.0f, 0.0f, 0u, 0u, 0u};
     if (SAMPLER >= 4) win = Window{pinned->wmx, pinned->wmy, pinned->wmz, pinned->whi, pinned->wsx, pinned->wsxy};
     const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_lut);
     Counters cnt = {0, 0, 0, 0, 0};
     run_tile_queue<COUNT>(a, [&](const RayView &v, int col, int row) {
-        return cast_ray<SAMPLER, COUNT, SHADE, CLAMP>(a, v, vs, win, lut_addr, s_esl, &s_esl_pin, step, threshold, col, row, cnt);
+        return cast_ray<SAMPLER, COUNT, SHADE, CLAMP, ZS>(a, v, vs, win, lut_addr, s_esl, &s_esl_pin, step, threshold, zero_lim, col, row, cnt);
     });
     if (COUNT) {
         unsigned long long v[5] = {cnt.rays_hit, cnt.rays_accum, cnt.esl_iters, cnt.samples, cnt.shaded};

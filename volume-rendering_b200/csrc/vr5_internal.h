@@ -20,6 +20,8 @@ struct vr5_renderer {
     uint32_t *d_esl = nullptr;    // 1024 words
     bool have_tf = false;
     bool tf_opaque = false;       // some TF entry has alpha >= 0.999 (a single sample can terminate a ray)
+    int tf_zero_prefix = 0;       // leading TF entries that are all-zero, when every alpha lies in [0, 1] and all values are finite (else 0)
+    int last_zskip = 0;           // the last cast_kernel launch was a zero-skip (ZS) build
     bool tf_can_shade = false;    // some TF entry has alpha > 0.05 (CPURenderer.cpp:32)
     // volume
     uint8_t *d_vol_linear = nullptr;  // always kept: source of every layout, of vr5_get_volume and of the min/max builder
@@ -99,6 +101,7 @@ struct vr5_renderer {
         bool host_single = false;   // VR5_HOST_SINGLE: the blocking host-buffer call renders the frame with one launch + one copy (no chunks)
         bool esl_exact = false;     // VR5_ESL_EXACT: the leading empty-space loop divides in every iteration (no predicted leaps)
         bool no_p2 = false;         // VR5_NO_P2: never build the power-of-two window
+        bool no_zskip = false;      // VR5_NO_ZSKIP: samples of the TF's all-zero prefix are composited like any other (no ZS kernels)
         int p2_wide = 0;            // VR5_P2_WIDE: 1 = 64-bit window addressing (kP2Wide) also below 4 GiB, -1 = never (texture alone)
         uint32_t win_sx = 0;        // VR5_WIN_SX: row stride of the window layouts (0 = default)
     } opt;

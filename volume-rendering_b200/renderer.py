@@ -172,6 +172,10 @@ class GPURenderer5:
         """VR5_SAMPLER_* id of the kernel variant the last launch used (see vr5_last_variant)."""
         return self._L.vr5_last_variant(self._h)
 
+    def last_zero_skip(self) -> int:
+        """1 when the last nearest-neighbour launch skipped the compositing of samples in the TF's all-zero prefix."""
+        return self._L.vr5_last_zero_skip(self._h)
+
     def synth_volume(self, kind: int, n: int, seed: int):
         self._check(self._L.vr5_synth_volume(self._h, kind, n, seed))
 
