@@ -680,6 +680,11 @@ def run_b200_arm(args, wl):
     # -- a single frame's launch alone (per-launch CUDA events on its stream): what one vr5_render call costs on the device ----
     scratch = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
     k_ms = gpu.render_timed(frames, scratch.data_ptr(), l2_flush=False)
+    gpu.set_option("VR5_LEAP_STATS", "1")   # counted in an untimed pass of their own: the counters are two contended atomics per leap
+    gpu.leap_stats()
+    gpu.render_timed(frames, scratch.data_ptr(), l2_flush=False)
+    leaps_k, left_out_k = gpu.leap_stats()   # over exactly these K frames of this rank
+    gpu.set_option("VR5_LEAP_STATS", "0")
     k_ms_flushed = gpu.render_timed(frames[: min(len(frames), 24)], scratch.data_ptr(), l2_flush=True)
     full_ms = None
     if rank == 0 and world > 1:    # the whole frame on one GPU, for `ideal = full / N`
@@ -723,11 +728,18 @@ def run_b200_arm(args, wl):
     line = None
     if rank == 0:
         value = samples_total / (ms * 1e-3) / 1e9
+        zero_skip = None
+        if not args.sampler.startswith("trilinear") and gpu.last_zero_skip() == 1:
+            zero_skip = {"leaps_per_frame": leaps_k / len(frames), "samples_left_out_per_frame": left_out_k / len(frames),
+                         "fraction_of_samples_left_out": left_out_k / max(samples_local, 1),
+                         "note": "the transfer function starts with all-zero entries: samples that classify to them skip their compositing, and runs of them "
+                                 "inside bricks whose maximum is such a value are leapt over (vr5_leap_stats; this rank's share). `value` counts the "
+                                 "REFERENCE's samples (the instrumented kernel's count, equal to the CPU checker's), not the fetches this kernel issues"}
         kernel_name = ("vr5::tri_kernel<variant %d>" % gpu.last_variant() if args.sampler.startswith("trilinear") else "vr5::cast_kernel<%s, variant %d%s>" % (args.sampler, gpu.last_variant(), ", zero-skip" if gpu.last_zero_skip() == 1 else ""))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": len(warm),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "fps": args.steps / (ms * 1e-3),
+            "dtype": "f32", "data": "synthetic", "fps": args.steps / (ms * 1e-3), "zero_skip": zero_skip,
             "ms_per_step_note": ("time of the K-frame sequence launch / K" if submission == "sequence" else "time of K frames submitted one launch each over %d frame lanes / K" % lanes) +
                                 ": a throughput under overlap, not the latency of one frame; roofline.single_frame_launch_ms is the latter",
             "config": {"workload": wl["name"] if not args.volume_file else "%s %s" % (rig.volume_route["file"], "x".join(map(str, rig.volume_route["dims"]))),

@@ -143,7 +143,7 @@ int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames,
 #define VR5_NOALLOC_MAX_FRAMES 256
 int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev);
 /* Experiment knobs by name (the VR5_* environment variables vr5_create reads ONCE: VR5_QUEUE_ORDER = rows | cols | rings,
- * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_NO_ZSKIP, VR5_P2_WIDE = 1 | -1 (64-bit window addressing for every volume | never), VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
+ * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_NO_ZSKIP, VR5_NO_LEAP, VR5_LEAP_BRICK, VR5_P2_WIDE = 1 | -1 (64-bit window addressing for every volume | never), VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
  * loop divides in every iteration, VR5_HOST_SINGLE = the blocking host-buffer call uses one launch + one copy). No effect on
  * the pixels. (VR5_SEQ_DEBUG is a measurement knob of the ring hand-shake that BREAKS the protocol: never set it in production.) */
 int vr5_set_option(vr5_renderer *r, const char *name, const char *value);
@@ -169,6 +169,12 @@ int vr5_sync_lane(vr5_renderer *r, int lane);
 int vr5_render_timed(vr5_renderer *r, const vr5_params *frames, int n_frames, void *out_dev_rgba8, int l2_flush, float *ms_out);
 /* Run the instrumented variant of the kernel on one frame and return its work counters (no framebuffer needed). */
 int vr5_count(vr5_renderer *r, const vr5_params *p, vr5_counters *out);
+/* Leaps over transparent bricks taken by the zero-skip kernels since the last call (out[0]) and the samples they left out (out[1]):
+ * the reference marches through empty space sample by sample after its leading loop (CPURenderer.cpp:28-39); here a run of samples
+ * that provably read voxels of a brick whose maximum classifies to an all-zero TF entry is left out, and the ray parameter after
+ * it is the one the reference's sequential k += step would hold. Waits for the handle's work; resets the counters.
+ * VR5_NO_LEAP=1 (read at the next volume / sampler change) turns the leaps off, VR5_LEAP_BRICK = log2 of the brick edge. Same pixels. */
+int vr5_leap_stats(vr5_renderer *r, uint64_t out[2]);
 /* Number of kernels this handle has launched so far (render, count, layout, synth). */
 uint64_t vr5_launch_count(const vr5_renderer *r);
 /* Pinned host memory for the end-to-end path (cudaHostAlloc / cudaFreeHost). */

@@ -128,3 +128,12 @@ def test_predicted_empty_space_leap_acceptance_rule(tmp_path):
     subprocess.run(["gcc", "-O2", "-ffp-contract=off", os.path.join(ROOT, "tools", "check_esl_predict.c"), "-o", str(exe), "-lm"], check=True)
     out = subprocess.run([str(exe), "5"], check=True, capture_output=True, text=True).stdout
     assert " 0 mismatches" in out, out
+
+
+def test_constant_increment_of_the_ray_parameter(tmp_path):
+    """The leaps of the zero-skip kernels (vr5_cast.cuh, try_leap) replace n sequential k += step of CPURenderer.cpp:37 by
+    bits(k) + n * M inside one binade; tools/check_kleap.c walks random and adversarial (k, step) pairs step by step and compares."""
+    exe = tmp_path / "check_kleap"
+    subprocess.run(["gcc", "-O2", "-ffp-contract=off", os.path.join(ROOT, "tools", "check_kleap.c"), "-o", str(exe), "-lm"], check=True)
+    out = subprocess.run([str(exe), "20000"], check=True, capture_output=True, text=True).stdout
+    assert "mismatches 0" in out and "steps compared 0" not in out, out

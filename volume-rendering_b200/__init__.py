@@ -87,6 +87,7 @@ def lib() -> C.CDLL:
         "vr5_get_sampler": (C.c_int, [vp]),
         "vr5_last_variant": (C.c_int, [vp]),
         "vr5_last_zero_skip": (C.c_int, [vp]),
+        "vr5_leap_stats": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
         "vr5_render": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),
         "vr5_render_raycaster": (C.c_int, [vp, vp, vp, C.c_int]),
         "vr5_render_async": (C.c_int, [vp, C.POINTER(Params), vp, C.c_int]),

@@ -109,6 +109,10 @@ struct KArgs {
     float step, threshold;
     float shade_alpha;       // 0.05f when light_kd > 0.01f else +inf: folds the uniform half of CPURenderer.cpp:32
     uint32_t zero_lim;       // ZS kernels: voxel values below it classify to an all-zero TF entry (host: fill_args); 0 = none
+    const uint8_t *brick_max;// ZS kernels: maximum voxel value per brick of (1 << brick_lb)^3 voxels (x fastest), or NULL: no leaps
+    uint32_t brick_lb, brick_nx, brick_ny, brick_nz;   // log2 of the brick edge, bricks per axis
+    unsigned long long *leap_stats;   // [0] leaps taken, [1] samples left out by them; NULL unless VR5_LEAP_STATS is set (contended atomics)
+    float leap_margin;       // voxels a leap keeps away from the faces of its brick: 4 x the bound of the reference's position error
     float kd;
     int esl;
     uint32_t bd_magic;       // ceil(2^32 / esl_block_dims): exact idx / bd for idx < 2^16 via umulhi
@@ -499,13 +503,115 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
         ks[j] = fadd(ks[j - 1], step);
         ss[j] = fetch(FetchTag<S0 == 2 ? (is_p2(SAMPLER) ? 6 : 2) : S0>(), ks[j]);
     }
+    // ---- leaps over transparent bricks (ZS kernels, a.brick_max != NULL) --------------------------------------------------------
+    // The reference marches through empty space sample by sample once it has met its first non-empty block (its leaps,
+    // RaycasterBase.h:67-85, only run in the leading loop). Under ZS such samples are no-ops, so a run of them may be left out
+    // altogether IF the ray parameter afterwards is the one the reference's sequential k += step would hold. It is computable:
+    // while k stays inside one binade [2^e, 2^(e+1)), k is a multiple of u = 2^(e-23) and RN(k + step) adds the SAME multiple
+    // M * u every time (step = q * u + r rounds the same way for every k; excluded: r == u / 2 exactly, where ties-to-even
+    // alternates) - so n steps on, the bit pattern of k is bits(k) + n * M, exactly (tools/check_kleap.c: 1.6e10 steps compared).
+    // Which samples may go: all that provably read a voxel of a brick whose maximum is below zero_lim. From the transparent sample at
+    // kc (voxel position v, inside brick b shrunk by a margin on every side) the ray stays inside the shrunk brick for t more units of k; samples
+    // 1 .. n = floor(t / inc) lie inside the shrunk brick in exact arithmetic, and the reference's own fp32 position of each of them
+    // is off by less than a quarter of the margin (host: fill_args derives the margin from |origin| and the dims), so each reads a voxel of b. The march continues with
+    // the sample at k + n * inc, fetched and classified like any other. Returns 0: brick not transparent / cannot tell, 1: too close
+    // to the brick's exit (or the binade's end) to gain anything, 2: kn = the ray parameter n >= 2 steps on.
+    auto try_leap = [&](const float kc, const float ka, float &kn) -> int {
+        const uint32_t kb = __float_as_uint(kc), kab = __float_as_uint(ka);
+        const uint32_t M = kab - kb;                                       // ka = RN(kc + step): M * u in the binade of kc
+        if ((kb ^ kab) >= 0x00800000u || (kb >> 23) < 30u || M == 0u) return 1;   // other binade (or kc tiny / zero): march
+        const float inc = ka - kc;                                         // exact
+        if (fabsf(step - inc) == __uint_as_float((kb & 0x7f800000u) - (24u << 23))) return 0;   // r == u / 2: no constant increment
+        const float vx = (ox + dx * kc + 1.0f) * vs.hx, vy = (oy + dy * kc + 1.0f) * vs.hy, vz = (oz + dz * kc + 1.0f) * vs.hz;
+        // (a position rounding has pushed outside the grid - negative, NaN: the conversion gives 0; beyond the last brick: clamped -
+        // fails the margin test below against the brick it is assigned to)
+        const uint32_t lb = a.brick_lb;
+        const uint32_t bx = min((uint32_t)vx >> lb, a.brick_nx - 1u), by = min((uint32_t)vy >> lb, a.brick_ny - 1u), bz = min((uint32_t)vz >> lb, a.brick_nz - 1u);
+        if (__ldg(a.brick_max + ((size_t)bz * (a.brick_nx * a.brick_ny) + by * a.brick_nx + bx)) >= zero_lim) return 0;
+        const float B = (float)(1u << lb), lx = (float)(bx << lb), ly = (float)(by << lb), lz = (float)(bz << lb);
+        const float sx = dx * vs.hx, sy = dy * vs.hy, sz = dz * vs.hz;     // voxels per unit of k
+        auto rcp_approx = [](float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; };
+        // time (in k, from kc) at which the ray leaves the SHRUNK brick per axis. The sample itself must lie inside the shrunk brick on
+        // every side: a ray that runs almost parallel to a face it has just crossed may, in the reference's arithmetic, stay on the
+        // other side of it for many more samples. A component of zero never leaves.
+        const float mg = a.leap_margin, inf = __uint_as_float(0x7f800000u);
+        float gap_min = 1.0f;
+        auto exit_k = [&](float v, float lo, float sv, float r) -> float {
+            const float hi_gap = (lo + B - mg) - v, lo_gap = v - (lo + mg);
+            gap_min = fminf(gap_min, fminf(hi_gap, lo_gap));
+            return sv != 0.0f ? (sv > 0.0f ? hi_gap : lo_gap) * r : inf;
+        };
+        const float rx = rcp_approx(fabsf(sx)), ry = rcp_approx(fabsf(sy)), rz = rcp_approx(fabsf(sz));
+        float tx = exit_k(vx, lx, sx, rx), ty = exit_k(vy, ly, sy, ry), tz = exit_k(vz, lz, sz, rz);
+        if (!(gap_min >= 0.0f)) return 1;                                  // inside a margin (or NaN): march on
+        // From brick to brick (3-D DDA on the shrunk exit times) while the next brick is transparent too and the crossing is CLEAN: the
+        // ray must be back inside the next brick's shrunk interior (2 * mg further along the crossing axis) before it leaves the
+        // shrunk range of either other axis - then every sample of the crossing lies within mg of that one face only and reads a
+        // voxel of one of the two bricks. t1 = exit time of the last brick accepted.
+        const uint32_t nbx = a.brick_nx, nby = a.brick_ny, nbz = a.brick_nz;
+        const uint8_t *bm = a.brick_max;
+        uint32_t ix = bx, iy = by, iz = bz;
+        const float t_max = k_far - kc;
+        float t1 = 0.0f;
+#pragma unroll 1
+        for (int hop = 0; hop < 48; hop++) {
+            t1 = fminf(tx, fminf(ty, tz));
+            if (!(t1 < t_max)) break;                                      // (also NaN)
+            if (tx <= ty && tx <= tz) {
+                if (!(t1 + 2.0f * mg * rx <= fminf(ty, tz))) break;
+                ix += sx > 0.0f ? 1u : 0xffffffffu;
+                if (ix >= nbx || __ldg(bm + ((size_t)iz * (nbx * nby) + iy * nbx + ix)) >= zero_lim) break;
+                tx += B * rx;
+            } else if (ty <= tz) {
+                if (!(t1 + 2.0f * mg * ry <= fminf(tx, tz))) break;
+                iy += sy > 0.0f ? 1u : 0xffffffffu;
+                if (iy >= nby || __ldg(bm + ((size_t)iz * (nbx * nby) + iy * nbx + ix)) >= zero_lim) break;
+                ty += B * ry;
+            } else {
+                if (!(t1 + 2.0f * mg * rz <= fminf(tx, ty))) break;
+                iz += sz > 0.0f ? 1u : 0xffffffffu;
+                if (iz >= nbz || __ldg(bm + ((size_t)iz * (nbx * nby) + iy * nbx + ix)) >= zero_lim) break;
+                tz += B * rz;
+            }
+        }
+        if (!(t1 >= 0.0f)) return 1;
+        t1 = fminf(t1, t_max);   // never past the ray's own end (a brick may overhang the grid): the landing sample is at most one step beyond k_far
+        // samples 1 .. n lie inside the bricks accepted; the march continues with sample n + 1 - inside the binade: bits(k) + (n + 1) * M
+        // must stay below the next power of two (two steps of room)
+        float nf = floorf(t1 * rcp_approx(inc) * 0.99999f);
+        const float nb = floorf((float)(0x007fffffu - (kb & 0x007fffffu)) * rcp_approx((float)M) * 0.99999f) - 3.0f;
+        nf = fminf(nf, nb);
+        if (!(nf >= 2.0f)) return 1;                                        // (false for NaN)
+        nf += 1.0f;
+        const uint32_t knb = kb + (uint32_t)nf * M;
+        if ((knb ^ kb) >= 0x00800000u) return 1;
+        kn = __uint_as_float(knb);
+        if (a.leap_stats) {   // VR5_LEAP_STATS (tests, bench): two atomics on one address per leap - never in a timed run
+            atomicAdd(a.leap_stats, 1ull);
+            atomicAdd(a.leap_stats + 1, (unsigned long long)nf - 1ull);   // samples 1 .. n are never fetched (nf = n + 1 here)
+        }
+        return 2;
+    };
+    // Leaps are tried in every SECOND stage of the unrolled march only, by all lanes of a warp whose sample is transparent at once
+    // (the lanes of a warp run the same stage at the same time: a warp-wide attempt costs what one lane's does) - unless the lane is
+    // backing off after a brick that was not transparent: `cool` = attempts to sit out (no brick table: all of them).
+    uint32_t cool = (ZS && a.brick_max) ? 0u : 0x7fffffffu;
     // one march step: returns true when the ray is finished
-    auto stage = [&](auto fetch_tag, uint32_t &s_cur, float &k_cur, const float k_last, const float &k_next) -> bool {
-        const float ka = fadd(k_last, step);
-        const uint32_t sn = fetch(fetch_tag, ka);
+    auto stage = [&](auto fetch_tag, auto leap_tag, uint32_t &s_cur, float &k_cur, const float k_last, const float &k_next) -> bool {
+        float ka = fadd(k_last, step);
+        uint32_t sn = fetch(fetch_tag, ka);
         if (COUNT) cnt.samples++;
         bool ended = false;
-        if (!(ZS && s_cur < zero_lim)) {  // ZS: a transparent sample has nothing to composite (see ZS above)
+        if (ZS && s_cur < zero_lim) {     // ZS: a transparent sample has nothing to composite (see ZS above)
+            if (kPrefetch == 1 && decltype(leap_tag)::value) {
+                if (cool == 0u) {
+                    float kn;
+                    const int got = try_leap(k_cur, ka, kn);
+                    if (got == 2) { ka = kn; sn = fetch(fetch_tag, kn); }
+                    else if (got == 0) cool = 3u;   // not a transparent brick: sit out three attempts (six samples)
+                } else cool--;
+            }
+        } else {
             float4 c = lut_fetch(lut_addr, s_cur);  // lut[s] == transfer_fn[s / TF_RATIO]
             if (SHADE && c.w > a.shade_alpha) {  // Raycaster::shade (RaycasterBase.h:87-98)
                 const float px = fadd(ox, fmul(dx, k_cur)), py = fadd(oy, fmul(dy, k_cur)), pz = fadd(oz, fmul(dz, k_cur));  // the sample's point
@@ -533,7 +639,7 @@ __device__ __forceinline__ uint32_t cast_ray(const KArgs &a, const RayView &v, c
         return ended || !((kPrefetch > 1 ? k_next : ka) <= k_far);  // while (k <= k_far) for the NEXT sample
     };
     // stage u of the unrolled loop works on slot u % kPrefetch; its fetch path follows the sampler's pattern
-#define VR5_STAGE(TAG, U) stage(FetchTag<TAG>(), ss[(U) % kPrefetch], ks[(U) % kPrefetch], ks[((U) + kPrefetch - 1) % kPrefetch], ks[((U) + 1) % kPrefetch])
+#define VR5_STAGE(TAG, U) stage(FetchTag<TAG>(), FetchTag<(U) & 1>(), ss[(U) % kPrefetch], ks[(U) % kPrefetch], ks[((U) + kPrefetch - 1) % kPrefetch], ks[((U) + 1) % kPrefetch])
     if (is_p2(SAMPLER)) {
         if (p2_mode(SAMPLER) == 0) {
             for (;;) {

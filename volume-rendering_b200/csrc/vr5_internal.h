@@ -20,6 +20,8 @@ struct vr5_renderer {
     uint32_t *d_esl = nullptr;    // 1024 words
     bool have_tf = false;
     bool tf_opaque = false;       // some TF entry has alpha >= 0.999 (a single sample can terminate a ray)
+    uint8_t *d_brick_max = nullptr;   // maximum voxel value per brick (build_brick_max), or NULL
+    uint32_t brick_lb = 0, brick_nx = 0, brick_ny = 0, brick_nz = 0;
     int tf_zero_prefix = 0;       // leading TF entries that are all-zero, when every alpha lies in [0, 1] and all values are finite (else 0)
     int last_zskip = 0;           // the last cast_kernel launch was a zero-skip (ZS) build
     bool tf_can_shade = false;    // some TF entry has alpha > 0.05 (CPURenderer.cpp:32)
@@ -65,6 +67,7 @@ struct vr5_renderer {
     cudaStream_t launch_stream = nullptr;  // set by launch() for launch_one()
     uint32_t last_grid = 0;
     void *d_counters = nullptr;
+    void *d_leap_stats = nullptr;   // two 64-bit counters: leaps taken by the zero-skip kernels, samples they left out
     // partition
     int rank = 0, world = 1, packed = 0;
     int band_first = 0, band_count = -1;   // >= 0: contiguous band of 4-row strips instead of the interleaved ones (vr5_set_partition_band)
@@ -101,6 +104,9 @@ struct vr5_renderer {
         bool host_single = false;   // VR5_HOST_SINGLE: the blocking host-buffer call renders the frame with one launch + one copy (no chunks)
         bool esl_exact = false;     // VR5_ESL_EXACT: the leading empty-space loop divides in every iteration (no predicted leaps)
         bool no_p2 = false;         // VR5_NO_P2: never build the power-of-two window
+        bool leap_stats = false;    // VR5_LEAP_STATS: the zero-skip kernels count their leaps (vr5_leap_stats; contended atomics: not for timed runs)
+        bool no_leap = false;       // VR5_NO_LEAP: the zero-skip kernels march through transparent bricks sample by sample (no brick table)
+        int leap_brick_log2 = 0;    // VR5_LEAP_BRICK: log2 of the brick edge of that table (0 = default: <= 32 bricks per axis, edge >= 8)
         bool no_zskip = false;      // VR5_NO_ZSKIP: samples of the TF's all-zero prefix are composited like any other (no ZS kernels)
         int p2_wide = 0;            // VR5_P2_WIDE: 1 = 64-bit window addressing (kP2Wide) also below 4 GiB, -1 = never (texture alone)
         uint32_t win_sx = 0;        // VR5_WIN_SX: row stride of the window layouts (0 = default)

@@ -51,6 +51,27 @@ __global__ void brick_layout_kernel(const uint8_t *__restrict__ lin, uint8_t *__
     }
 }
 
+// linear -> maximum voxel value per brick of (1 << lb)^3 voxels (x fastest), one warp per brick: the table the zero-skip kernels
+// consult before they leap over a brick in which every sample would be a transparent one (vr5_cast.cuh, try_leap)
+__global__ void brick_max_kernel(const uint8_t *__restrict__ lin, uint8_t *__restrict__ bmax, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t lb,
+                                 uint32_t nbx, uint32_t nby, uint32_t nbz) {
+    const uint32_t lane = threadIdx.x & 31u, B = 1u << lb;
+    const uint64_t n_bricks = (uint64_t)nbx * nby * nbz;
+    for (uint64_t b = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < n_bricks; b += ((uint64_t)gridDim.x * blockDim.x) >> 5) {
+        const uint32_t bx = (uint32_t)(b % nbx), by = (uint32_t)((b / nbx) % nby), bz = (uint32_t)(b / ((uint64_t)nbx * nby));
+        const uint32_t x0 = bx << lb, y0 = by << lb, z0 = bz << lb;
+        uint32_t m = 0;
+        for (uint32_t row = lane; row < B * B; row += 32u) {   // a lane takes whole x-rows of the brick
+            const uint32_t y = y0 + (row & (B - 1u)), z = z0 + (row >> lb);
+            if (y >= ny || z >= nz) continue;
+            const uint8_t *src = lin + ((uint64_t)z * ny + y) * nx;
+            for (uint32_t x = x0; x < min(x0 + B, nx); x++) m = max(m, (uint32_t)src[x]);
+        }
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) bmax[b] = (uint8_t)m;
+    }
+}
+
 // linear -> linear padded by one replicated voxel at the upper end of every axis (source of the 3-D texture: lets the
 // march drop its upper index clamp, see sample_volume<.., CLAMP=false>)
 __global__ void pad_edge_kernel(const uint8_t *__restrict__ lin, uint8_t *__restrict__ padded, uint32_t nx, uint32_t ny, uint32_t nz) {
@@ -228,6 +249,8 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
     }
     if ((e = cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaMalloc(&r->d_counters, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc counters", e);
+    if ((e = cudaMalloc(&r->d_leap_stats, 16)) != cudaSuccess) return bail("cudaMalloc leap statistics", e);
+    if ((e = cudaMemset(r->d_leap_stats, 0, 16)) != cudaSuccess) return bail("cudaMemset leap statistics", e);
     if ((e = cudaMalloc(&r->d_seq_queue, 128)) != cudaSuccess) return bail("cudaMalloc sequence queue", e);
     if ((e = cudaMemset(r->d_seq_queue, 0, 128)) != cudaSuccess) return bail("cudaMemset sequence queue", e);
     if ((e = cudaStreamCreateWithFlags(&r->consumer_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate consumer", e);
@@ -240,7 +263,7 @@ extern "C" int vr5_create(int device, vr5_renderer **out) {
         cudaGetLastError();
     }
     // experiment knobs: the environment is read here, once; the launch path only looks at r->opt (vr5_set_option changes it)
-    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_NO_ZSKIP", "VR5_P2_WIDE", "VR5_WIN_SX", "VR5_ESL_EXACT", "VR5_SEQ_DEBUG", "VR5_HOST_SINGLE"})
+    for (const char *name : {"VR5_QUEUE_ORDER", "VR5_ROW_MAJOR", "VR5_WARP_FETCH", "VR5_TRI_CLAMPED", "VR5_TRIF_CTAS", "VR5_TRIF_DEPTH", "VR5_NO_P2", "VR5_NO_ZSKIP", "VR5_NO_LEAP", "VR5_LEAP_BRICK", "VR5_LEAP_STATS", "VR5_P2_WIDE", "VR5_WIN_SX", "VR5_ESL_EXACT", "VR5_SEQ_DEBUG", "VR5_HOST_SINGLE"})
         if (const char *v = getenv(name)) vr5_set_option(r, name, v);
     r->err.clear();
     const char *env = getenv("VR5_SAMPLER");
@@ -311,6 +334,7 @@ static void free_layouts(vr5_renderer *r) {
     if (r->d_vol_padded) { cudaFree(r->d_vol_padded); r->d_vol_padded = nullptr; }
     if (r->d_vol_window) { cudaFree(r->d_vol_window); r->d_vol_window = nullptr; }
     if (r->d_cells) { cudaFree(r->d_cells); r->d_cells = nullptr; }
+    if (r->d_brick_max) { cudaFree(r->d_brick_max); r->d_brick_max = nullptr; }
     free_p2(r);
 }
 
@@ -336,6 +360,7 @@ extern "C" void vr5_destroy(vr5_renderer *r) {
     cudaFree(r->d_tf);
     cudaFree(r->d_esl);
     cudaFree(r->d_counters);
+    cudaFree(r->d_leap_stats);
     cudaFree(r->d_flush);
     if (r->own_stream) cudaStreamDestroy(r->own_stream);
     delete r;
@@ -555,9 +580,30 @@ static int build_p2(vr5_renderer *r) {
 
 static inline bool is_trilinear(int sampler) { return sampler == VR5_SAMPLER_TRILINEAR || sampler == VR5_SAMPLER_TRILINEAR_FMA; }
 
+// per-brick maxima for the leaps of the zero-skip kernels: brick edge 2^lb voxels, at most 32 bricks per axis by default (a table
+// of <= 32 KiB, L1-resident: an attempt costs ~100 instructions, so a leap must be worth a few dozen samples), VR5_LEAP_BRICK = log2 of the edge overrides it; VR5_NO_LEAP: no table, no leaps
+static int build_brick_max(vr5_renderer *r) {
+    if (r->opt.no_leap) return 0;
+    const uint32_t nmax = std::max<uint32_t>(r->nx, std::max<uint32_t>(r->ny, r->nz));
+    uint32_t lb = 3;
+    while (((nmax + (1u << lb) - 1u) >> lb) > 32u) lb++;
+    if (r->opt.leap_brick_log2 >= 2 && r->opt.leap_brick_log2 <= 10) lb = (uint32_t)r->opt.leap_brick_log2;
+    r->brick_lb = lb;
+    r->brick_nx = (r->nx + (1u << lb) - 1u) >> lb; r->brick_ny = (r->ny + (1u << lb) - 1u) >> lb; r->brick_nz = (r->nz + (1u << lb) - 1u) >> lb;
+    const uint64_t bytes = (uint64_t)r->brick_nx * r->brick_ny * r->brick_nz;
+    cudaError_t e = cudaMalloc(&r->d_brick_max, bytes);
+    if (e != cudaSuccess) { vr5_fail(r, "cudaMalloc brick maxima", e, __FILE__, __LINE__); cudaGetLastError(); r->d_brick_max = nullptr; return 1; }
+    brick_max_kernel<<<r->num_sms * 8, 256, 0, r->stream>>>(r->d_vol_linear, r->d_brick_max, r->nx, r->ny, r->nz, lb, r->brick_nx, r->brick_ny, r->brick_nz);
+    r->launches++;
+    VR5_CUDA(r, cudaGetLastError());
+    VR5_CUDA(r, cudaStreamSynchronize(r->stream));
+    return 0;
+}
+
 static int build_layout(vr5_renderer *r) {
     free_layouts(r);
     if (!r->d_vol_linear) return 0;
+    if (!is_trilinear(r->sampler) && build_brick_max(r)) return 1;
     if (is_trilinear(r->sampler)) {
         const uint64_t bytes = (uint64_t)(r->nx + 1 + 2 * kTriGuard) * (r->ny + 1 + 2 * kTriGuard) * (r->nz + 1 + 2 * kTriGuard) * 8u;
         // the unclamped march wants the array inside one 4-GiB address window: an allocation that straddles one is retried
@@ -858,6 +904,9 @@ extern "C" int vr5_set_option(vr5_renderer *r, const char *name, const char *val
     else if (!strcmp(name, "VR5_SEQ_DEBUG")) r->opt.seq_debug = atoi(value);
     else if (!strcmp(name, "VR5_HOST_SINGLE")) r->opt.host_single = truthy();
     else if (!strcmp(name, "VR5_NO_ZSKIP")) r->opt.no_zskip = truthy();
+    else if (!strcmp(name, "VR5_NO_LEAP")) r->opt.no_leap = truthy();           // takes effect at the next layout build
+    else if (!strcmp(name, "VR5_LEAP_STATS")) r->opt.leap_stats = truthy();
+    else if (!strcmp(name, "VR5_LEAP_BRICK")) r->opt.leap_brick_log2 = atoi(value);   // log2 of the brick edge; next layout build
     else if (!strcmp(name, "VR5_NO_P2")) r->opt.no_p2 = truthy();        // takes effect at the next layout build
     else if (!strcmp(name, "VR5_P2_WIDE")) r->opt.p2_wide = strtol(value, nullptr, 10);   // 1 = force, -1 = never; next layout build
     else if (!strcmp(name, "VR5_WIN_SX")) r->opt.win_sx = (uint32_t)strtoul(value, nullptr, 10);
@@ -1012,6 +1061,23 @@ static int fill_args(vr5_renderer *r, const vr5_params *p, void *out_dev, KArgs 
     }
     a->counters = reinterpret_cast<Counters *>(r->d_counters);
     a->reach = frame_reach(*a);
+    // leaps over transparent bricks (zero-skip kernels, vr5_cast.cuh try_leap): the reference's fp32 position of a sample, o + d * k, + 1,
+    // * dims / 2, lies within err = 3 * 2^-24 * (|origin| + 2) * dims / 2 voxels (+ half an ulp of the product) of the exact point of
+    // the ray; a leap keeps 4 x that bound + 1/32 voxel (the rounding of its own brick-to-brick walk: < 0.01 voxel over 48 bricks) away
+    // from the faces of its bricks. Views for which that margin would exceed 1/4 voxel (huge grids seen from far away) march sample by sample.
+    a->brick_max = nullptr;
+    if (a->zero_lim && r->d_brick_max && std::isfinite(a->reach)) {
+        float ob = 0.0f;
+        const float ov[3] = {a->ox, a->oy, a->oz}, rv[3] = {a->rx, a->ry, a->rz}, uv[3] = {a->ux, a->uy, a->uz};
+        for (int i = 0; i < 3; i++)
+            ob = fmaxf(ob, fabsf(ov[i]) + (a->perspective ? 0.0f : fabsf(rv[i]) * (float)(a->half_w + 1) + fabsf(uv[i]) * (float)(a->half_h + 1)));
+        const float hmax = fmaxf(a->hx, fmaxf(a->hy, a->hz));
+        const float margin = 4.0f * (3.0f * 5.9604645e-8f * (ob + 2.0f) * hmax + 5.9604645e-8f * 2.0f * hmax) + 1.0f / 32.0f;
+        if (std::isfinite(ob) && margin <= 0.25f) {
+            a->brick_max = r->d_brick_max; a->brick_lb = r->brick_lb; a->brick_nx = r->brick_nx; a->brick_ny = r->brick_ny; a->brick_nz = r->brick_nz;
+            a->leap_margin = margin; a->leap_stats = r->opt.leap_stats ? reinterpret_cast<unsigned long long *>(r->d_leap_stats) : nullptr;
+        }
+    }
     // predicted leaps (vr5_cast.cuh, skip_leading_empty_space): finite, non-degenerate view, rays clipped to the cube [-1, 1]^3
     // the grid fills, step with a safe reciprocal; VR5_ESL_EXACT keeps the reference's divisions in every iteration
     int step_exp = 0;
@@ -1088,6 +1154,7 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
             KArgs ai;   // the unclamped variants must hold for every frame: carry the largest reach
             if (fill_args(r, &p, targets[i].out_dev, &ai)) return 1;
             a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
+            if (!ai.brick_max) a.brick_max = nullptr;   // ... and so must the position bound of the leaps
             band0 = (uint32_t)ai.rank; bandn = ai.tile_rows_local;
             if (bandn > max_rows) max_rows = bandn;
         }
@@ -1187,6 +1254,7 @@ extern "C" int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *fr
             KArgs ai;
             if (fill_args(r, &p, outs_dev[i], &ai)) return 1;
             a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
+            if (!ai.brick_max) a.brick_max = nullptr;   // ... and so must the position bound of the leaps
             band0 = (uint32_t)ai.rank; bandn = ai.tile_rows_local;
             if (bandn > max_rows) max_rows = bandn;
         }
@@ -1467,6 +1535,16 @@ extern "C" int vr5_count(vr5_renderer *r, const vr5_params *p, vr5_counters *out
     static_assert(sizeof(Counters) == sizeof(vr5_counters), "counter layout");
     VR5_CUDA(r, cudaMemcpyAsync(out, r->d_counters, sizeof(Counters), cudaMemcpyDeviceToHost, st));
     VR5_CUDA(r, cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int vr5_leap_stats(vr5_renderer *r, uint64_t out[2]) {
+    if (!r) return 1;
+    if (!out) { vr5_fail(r, "vr5_leap_stats: NULL out", cudaSuccess, __FILE__, __LINE__); return 1; }
+    VR5_CUDA(r, cudaSetDevice(r->device));
+    VR5_CUDA(r, sync_all(r));
+    VR5_CUDA(r, cudaMemcpy(out, r->d_leap_stats, 16, cudaMemcpyDeviceToHost));
+    VR5_CUDA(r, cudaMemset(r->d_leap_stats, 0, 16));
     return 0;
 }
 

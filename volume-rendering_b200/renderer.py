@@ -176,6 +176,12 @@ class GPURenderer5:
         """1 when the last nearest-neighbour launch skipped the compositing of samples in the TF's all-zero prefix."""
         return self._L.vr5_last_zero_skip(self._h)
 
+    def leap_stats(self):
+        """(leaps taken, samples left out) by the zero-skip kernels since the last call (vr5_leap_stats); resets the counters."""
+        out = (C.c_uint64 * 2)()
+        self._check(self._L.vr5_leap_stats(self._h, out))
+        return int(out[0]), int(out[1])
+
     def synth_volume(self, kind: int, n: int, seed: int):
         self._check(self._L.vr5_synth_volume(self._h, kind, n, seed))
 
