@@ -96,6 +96,7 @@ def test_leaps_off_and_in_sequences(port, R):
         try:
             g.set_option("VR5_NO_LEAP", off)
             g.set_option("VR5_LEAP_STATS", "1")
+            g.set_option("VR5_LEAP_BRICK", "3")   # (the default edge, 32, leaves a 96^3 volume 27 bricks: too few to count on an empty one)
             g.set_window_buffer(w, h)
             scene, _ = product_scene(R, scs[0])
             g.set_scene(scene)

@@ -580,12 +580,12 @@ static int build_p2(vr5_renderer *r) {
 
 static inline bool is_trilinear(int sampler) { return sampler == VR5_SAMPLER_TRILINEAR || sampler == VR5_SAMPLER_TRILINEAR_FMA; }
 
-// per-brick maxima for the leaps of the zero-skip kernels: brick edge 2^lb voxels, at most 32 bricks per axis by default (a table
+// per-brick maxima for the leaps of the zero-skip kernels: brick edge 2^lb voxels, lb >= 5 and at most 32 bricks per axis by default (a table
 // of <= 32 KiB, L1-resident: an attempt costs ~100 instructions, so a leap must be worth a few dozen samples), VR5_LEAP_BRICK = log2 of the edge overrides it; VR5_NO_LEAP: no table, no leaps
 static int build_brick_max(vr5_renderer *r) {
     if (r->opt.no_leap) return 0;
     const uint32_t nmax = std::max<uint32_t>(r->nx, std::max<uint32_t>(r->ny, r->nz));
-    uint32_t lb = 3;
+    uint32_t lb = 5;   // edge 32 at least: a hop of the brick-to-brick walk costs ~25 instructions and a table look-up (C4: edge 16 gains nothing, 8 loses)
     while (((nmax + (1u << lb) - 1u) >> lb) > 32u) lb++;
     if (r->opt.leap_brick_log2 >= 2 && r->opt.leap_brick_log2 <= 10) lb = (uint32_t)r->opt.leap_brick_log2;
     r->brick_lb = lb;
