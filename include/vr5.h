@@ -143,7 +143,7 @@ int vr5_render_sequence(vr5_renderer *r, const vr5_params *frames, int n_frames,
 #define VR5_NOALLOC_MAX_FRAMES 256
 int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *frames, int n_frames, void *const *outs_dev);
 /* Experiment knobs by name (the VR5_* environment variables vr5_create reads ONCE: VR5_QUEUE_ORDER = rows | cols | rings,
- * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_NO_ZSKIP, VR5_NO_LEAP, VR5_LEAP_BRICK, VR5_P2_WIDE = 1 | -1 (64-bit window addressing for every volume | never), VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
+ * VR5_WARP_FETCH, VR5_TRI_CLAMPED, VR5_TRIF_CTAS, VR5_TRIF_DEPTH, VR5_NO_P2, VR5_NO_ZSKIP, VR5_NO_LEAP, VR5_LEAP_BRICK, VR5_LEAP_STATS (the zero-skip kernels count their leaps for vr5_leap_stats: contended atomics, not for timed runs), VR5_P2_WIDE = 1 | -1 (64-bit window addressing for every volume | never), VR5_WIN_SX, VR5_ESL_EXACT = the leading empty-space
  * loop divides in every iteration, VR5_HOST_SINGLE = the blocking host-buffer call uses one launch + one copy). No effect on
  * the pixels. (VR5_SEQ_DEBUG is a measurement knob of the ring hand-shake that BREAKS the protocol: never set it in production.) */
 int vr5_set_option(vr5_renderer *r, const char *name, const char *value);
@@ -173,7 +173,9 @@ int vr5_count(vr5_renderer *r, const vr5_params *p, vr5_counters *out);
  * the reference marches through empty space sample by sample after its leading loop (CPURenderer.cpp:28-39); here a run of samples
  * that provably read voxels of a brick whose maximum classifies to an all-zero TF entry is left out, and the ray parameter after
  * it is the one the reference's sequential k += step would hold. Waits for the handle's work; resets the counters.
- * VR5_NO_LEAP=1 (read at the next volume / sampler change) turns the leaps off, VR5_LEAP_BRICK = log2 of the brick edge. Same pixels. */
+ * Counted only while the option VR5_LEAP_STATS is set (two atomics on one address per leap: never in a timed run). VR5_NO_LEAP=1 (read at
+ * the next volume / sampler change) turns the leaps off, VR5_LEAP_BRICK = log2 of the brick edge (default: 32 voxels, at most 32 bricks
+ * per axis). Same pixels either way. */
 int vr5_leap_stats(vr5_renderer *r, uint64_t out[2]);
 /* Number of kernels this handle has launched so far (render, count, layout, synth). */
 uint64_t vr5_launch_count(const vr5_renderer *r);
