@@ -5,6 +5,8 @@ whose maximum classifies to an all-zero TF entry and continues at the ray parame
 steps that are exact / inexact / ties in a binade, for ray parameters in several binades, both projections, ragged volumes - and the
 leap counters must show that leaps were actually taken (vr5_leap_stats).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -118,3 +120,36 @@ def test_leaps_off_and_in_sequences(port, R):
                 assert sha(out) == sha(ref)
         finally:
             g.close()
+
+
+def test_leaps_random_views(port, R):
+    """150 random views of a sparse volume - any angle, distance 1.05 .. 9 (ray parameters from ~0 up to 12: many binades), step factor
+    0.3 .. 2.5 (plus steps with few mantissa bits: exact sums and ties), both projections, two brick edges - bit-equal to the CPU checker."""
+    rng = np.random.default_rng(77)
+    vol = _sparse_volume((64, 80, 56), 41)
+    n = max(vol.shape)
+    step0 = float(np.float32(2.0) / np.float32(n) - np.float32(2.0) / np.float32(n) / np.float32(n))
+    tables = _tables(port)
+    w, h = 72, 56
+    leaps = 0
+    for lb in ("3", "4"):
+        g = R.GPURenderer5(0)
+        try:
+            g.set_option("VR5_LEAP_BRICK", lb)
+            g.set_option("VR5_LEAP_STATS", "1")
+            g.set_window_buffer(w, h)
+            for i in range(int(os.environ.get("VR5_LEAP_SOAK", "75"))):   # (a soak run: VR5_LEAP_SOAK=2000)
+                ang = (float(rng.uniform(-90, 90)), float(rng.uniform(0, 360)), float(rng.uniform(-30, 30)))
+                dist = float(rng.choice([1.05, 1.3, 2.0, 2.0, 3.1, 4.0, 6.5, 9.0]))
+                step = step0 * float(rng.uniform(0.3, 2.5))
+                if i % 5 == 0:   # few mantissa bits: exact in some binades, a tie in others
+                    step = float(np.float32(2.0 ** -6 + 2.0 ** -int(rng.integers(20, 27))))
+                persp = int(rng.integers(0, 2))
+                base = tables["opaque" if i % 2 else "thin"]
+                view = oracle.View.from_buffer_copy(bytes(R.camera(w, h, persp, ang, dist)))
+                frame, want, st = _render_both(g, R, port, vol, base, view, {"ray_step": step})
+                assert_parity(frame, want, exact=True, what=(lb, i, ang, dist, step, persp, st))
+                leaps += st[0]
+        finally:
+            g.close()
+    assert leaps > 1000, leaps
