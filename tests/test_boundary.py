@@ -112,8 +112,8 @@ def test_kernel_has_no_fused_multiply_add_in_ray_math():
             fn = line.split("Function :")[1].strip()
         elif "FFMA2" in line and fn:
             with_ffma2.add(fn)
-    # mangled template arguments of tri_kernel: COUNT, FAST, SHADE, FMA, MINB, DEPTH -> ...ILb?ELb?ELb?ELb1ELi?ELi?EE...
-    bad = [f for f in with_ffma2 if not re.search(r"tri_kernelILb[01]ELb[01]ELb[01]ELb1ELi\d+ELi\d+EE", f)]
+    # mangled template arguments of tri_kernel: COUNT, FAST, SHADE, FMA, MINB, DEPTH, ZS -> ...ILb?ELb?ELb?ELb1ELi?ELi?ELb?EE...
+    bad = [f for f in with_ffma2 if not re.search(r"tri_kernelILb[01]ELb[01]ELb[01]ELb1ELi\d+ELi\d+ELb[01]EE", f)]
     assert not bad, bad
     assert any("tri_kernel" in f for f in with_ffma2)  # the contracted march does use the packed FMA
     mk = open(os.path.join(CSRC, "Makefile")).read()

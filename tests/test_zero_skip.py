@@ -98,3 +98,37 @@ def test_zero_skip_in_sequences_and_lanes(port, R):
             assert sha(out) == sha(ref)
     finally:
         g.close()
+
+
+@pytest.mark.parametrize("policy", [("trilinear", True), ("trilinear-fma", "fma")], ids=["trilinear", "trilinear-fma"])
+@pytest.mark.parametrize("clamped", [False, True])
+def test_zero_skip_trilinear_policies(policy, clamped, port, R, monkeypatch):
+    """The trilinear policies (vr5_tri.cuh, GPURenderer4 semantics) skip the classification and compositing of samples whose TF
+    interpolation interval lies inside the table's all-zero prefix: bit-equal to the restated trilinear checker, skip on and off."""
+    if clamped:
+        monkeypatch.setenv("VR5_TRI_CLAMPED", "1")
+    sampler, mode = policy
+    g = R.GPURenderer5(0, sampler=sampler)
+    try:
+        for shape, seed in [((64, 64, 64), 15), ((37, 53, 70), 16)]:
+            vol = _volume(shape, seed)
+            vol[:, : shape[1] // 2] //= 3          # a region whose interpolated values stay inside the default table's zero prefix
+            for name, (base, expect_skip) in _tables(port).items():
+                for persp, ang, wh, kw in [(0, POSES[1], (163, 97), {}), (1, (20, 130, 0), (129, 131), {"esl": False}),
+                                           (0, POSES[0], (96, 64), {"threshold": 0.0}), (1, POSES[3], (64, 48), {"threshold": -0.5})]:
+                    view = oracle.View.from_buffer_copy(bytes(R.camera(wh[0], wh[1], persp, ang, 2.0)))
+                    sc = port.make_scene(vol, base, view, **kw)
+                    scene, params = product_scene(R, sc)
+                    want, cnt = port.render(sc, trilinear=mode)
+                    g.set_window_buffer(*wh)
+                    g.set_scene(scene)
+                    for off in ("0", "1"):
+                        g.set_option("VR5_NO_ZSKIP", off)
+                        frame = g.render_volume(params)
+                        skip = g.last_zero_skip()
+                        assert skip == (1 if (off == "0" and expect_skip and kw.get("threshold", 0.95) >= 0.0) else 0), (name, kw, off, skip)
+                        assert_parity(frame, want, exact=True, what=(sampler, clamped, shape, name, kw, "no_zskip=" + off))
+                    g.set_option("VR5_NO_ZSKIP", "0")
+                    assert g.count(params) == cnt
+    finally:
+        g.close()

@@ -112,7 +112,7 @@ struct vr5_renderer {
         uint32_t win_sx = 0;        // VR5_WIN_SX: row stride of the window layouts (0 = default)
     } opt;
     // bookkeeping
-    int ctas_per_sm[512] = {0};  // occupancy cache per kernel variant
+    int ctas_per_sm[520] = {0};  // occupancy cache per kernel variant
     uint64_t launches = 0;
     void *d_flush = nullptr;
     size_t flush_bytes = 0;

@@ -1330,15 +1330,27 @@ static int launch_variant(vr5_renderer *r, KArgs &a, bool count) {
             tri_kernel<false, true, false, true, 5>, tri_kernel<false, true, false, true, 4>,
             tri_kernel<false, true, false, true, 6, 2>, tri_kernel<false, true, false, true, 5, 2>, tri_kernel<false, true, false, true, 4, 2>,
             tri_kernel<false, true, false, true, 4, 3>, tri_kernel<false, true, false, true, 4, 4>};
-        int &per_sm = r->ctas_per_sm[480 + v];  // 480..496 (cast_kernel variants use 0..63)
+        // zero-skip builds of the variants that render frames (not the instrumented ones, not the register-budget experiments): chosen when
+        // the transfer function starts with all-zero entries (fill_args: zero_lim = 2 x the prefix, under the same conditions as for cast_kernel)
+        void (*const kernels_zs[17])(const KArgs, const TriArgs) = {
+            nullptr, tri_kernel<false, false, false, false, 6, 1, true>, tri_kernel<false, false, true, false, 0, 1, true>,
+            tri_kernel<false, true, false, false, 6, 1, true>, tri_kernel<false, true, true, false, 0, 1, true>,
+            nullptr, tri_kernel<false, false, false, true, 6, 1, true>, tri_kernel<false, false, true, true, 0, 1, true>,
+            tri_kernel<false, true, false, true, 6, 1, true>, tri_kernel<false, true, true, true, 0, 1, true>,
+            nullptr, nullptr, tri_kernel<false, true, false, true, 6, 2, true>, nullptr, nullptr, nullptr, nullptr};
+        const bool zs = a.zero_lim >= 2u && kernels_zs[v] != nullptr;
+        t.zero_um = zs ? kTriMagicBits + a.zero_lim / 2u - 1u : 0u;
+        void (*const kernel)(const KArgs, const TriArgs) = zs ? kernels_zs[v] : kernels[v];
+        int &per_sm = r->ctas_per_sm[480 + v + (zs ? 17 : 0)];  // 480..513 (cast_kernel variants use 0..215)
         if (per_sm == 0) {
-            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernels[v], kCtaThreads, 0);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kCtaThreads, 0);
             if (e != cudaSuccess || per_sm < 1) per_sm = 1;
         }
         uint32_t grid = (uint32_t)(r->num_sms * per_sm);
         const uint32_t needed = (a.n_queue * a.n_frames + (kCtaThreads / 32) - 1) / (kCtaThreads / 32);
         if (grid > needed) grid = needed ? needed : 1;
-        kernels[v]<<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
+        kernel<<<grid, kCtaThreads, 0, r->launch_stream>>>(a, t);
+        r->last_zskip = zs ? 1 : 0;
         r->tri_fast = fast ? 1 : 0;
         r->last_grid = grid;
         r->launches++;

@@ -23,6 +23,9 @@ struct TriArgs {
     // unclamped march (FAST): the array lies inside one 4-GiB address window and the low 32 address bits of the record of a
     // point are bz*s2 + by*s1 + bx*8 + c0 (mod 2^32), b = bit pattern of RD(t + magic) per axis
     uint32_t hi, c0, s1, s2;
+    // ZS kernels: a sample whose biased TF position floor, bits(RD(u + magic)), lies below this classifies to a pair of all-zero TF
+    // entries (both ends of its interpolation interval lie inside the table's all-zero prefix): it has nothing to composite
+    uint32_t zero_um;
 };
 
 // the march loop's uniform operands. With VR5_TRI_PIN they are read once per thread through a volatile shared copy, which
@@ -103,15 +106,17 @@ constexpr int kTriPairs = 129;
 // 2.4 shared-memory bank conflicts per warp-sample on gradient-rich frames).
 constexpr int kTriDiffOffset = kTriPairs * 16;  // byte offset of the difference table
 // pair_c = shared address of the table - ((bits(magic) - 1) << 4) (mod 2^32): the entry address is one shift-add of the bits
-__device__ __forceinline__ float4 tri_classify(uint32_t pair_c, float s) {
-    const float t = fsub(fmul(s, 128.0f), 0.5f);
-    const float tm = __fadd_rd(t, kTriMagic);
+__device__ __forceinline__ float4 tri_classify_at(uint32_t pair_c, float t, float tm) {   // t = TF position, tm = RD(t + magic)
     const float w = fsub(t, fsub(tm, kTriMagic));
     const uint32_t addr = pair_c + (__float_as_uint(tm) << 4);
     float4 a, d;
     asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(addr));
     asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w) : "r"(addr), "n"(kTriDiffOffset));
     return make_float4(fadd(a.x, fmul(w, d.x)), fadd(a.y, fmul(w, d.y)), fadd(a.z, fmul(w, d.z)), fadd(a.w, fmul(w, d.w)));
+}
+__device__ __forceinline__ float4 tri_classify(uint32_t pair_c, float s) {
+    const float t = fsub(fmul(s, 128.0f), 0.5f);
+    return tri_classify_at(pair_c, t, __fadd_rd(t, kTriMagic));
 }
 
 // ---- contracted arithmetic (VR5_SAMPLER_TRILINEAR_FMA) ----------------------------------------------------------------
@@ -225,7 +230,11 @@ __device__ __forceinline__ void trif_classify(uint32_t pair_c, float v, float2 &
     cba = __ffma2_rn(both(w), make_float2(d.z, d.w), make_float2(a.z, a.w));
 }
 
-template <bool COUNT, bool FAST, bool SHADE, bool FMA, int DEPTH>
+// ZS ("zero skip", as in vr5_cast.cuh): the host has seen that the transfer function starts with all-zero entries, that every alpha lies
+// in [0, 1] and the threshold is not negative. A sample whose interpolation interval of the TF lies inside that prefix gets the colour
+// 0 + w * 0 = 0 and leaves the accumulators as they are (acc + 0 * (1 - acc.a), or fma(0, 1 - acc.a, acc)): its table fetches, the
+// compositing and the shading test are skipped.
+template <bool COUNT, bool FAST, bool SHADE, bool FMA, int DEPTH, bool ZS = false>
 __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &rv, const TriArgs &t, const TriRegs &g, const uint32_t *esl_bits, const EslPin *esl_pin, int col, int row,
                                                  Counters &cnt) {
     // View::get_ray, Raycaster::intersect and the leading empty-space loop are those of the nearest path (vr5_cast.cuh)
@@ -294,12 +303,16 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &
                 tap.wxy = sub2(txy, __fadd2_rn(tm2, both(-kTriMagic)));
                 tap.wz = wzu.x;
                 trif_load(t, g, __float_as_uint(tm2.x), __float_as_uint(tm2.y), __float_as_uint(zum.x), true, tap.c);
+                if (ZS && __float_as_uint(zum.y) < t.zero_um) { kc = ka; return true; }   // transparent: acc.a is what it was, below the threshold
                 trif_classify_at(g.pair_c, __float_as_uint(zum.y), wzu.y, crg, cba);
             } else
 #endif
             {
                 tap = trif_request<FAST>(t, g, __ffma2_rn(dvxy, both(ka), ovxy), __fmaf_rn(dvz, ka, ovz));
-                trif_classify(g.pair_c, v, crg, cba);
+                const float u = __fmaf_rn(v, kTfScale255, -0.5f);
+                const float um = __fadd_rd(u, kTriMagic);
+                if (ZS && __float_as_uint(um) < t.zero_um) { if (COUNT) cnt.samples++; kc = ka; return true; }
+                trif_classify_at(g.pair_c, __float_as_uint(um), fsub(u, fsub(um, kTriMagic)), crg, cba);
             }
             if (COUNT) cnt.samples++;
             if (SHADE && cba.y > a.shade_alpha) {
@@ -346,24 +359,28 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &
         const float nx = fadd(ox, fmul(dx, kn)), ny = fadd(oy, fmul(dy, kn)), nz = fadd(oz, fmul(dz, kn));
         const TriTap next = tri_request<FAST>(t, g, nx, ny, nz);
         const float s = tri_resolve(tap);
-        float4 c = tri_classify(g.pair_c, s);
+        const float tpos = fsub(fmul(s, 128.0f), 0.5f);   // checker's classify_linear position
+        const float tpm = __fadd_rd(tpos, kTriMagic);
         if (COUNT) cnt.samples++;
-        // SHADE=false: the host has seen that no TF entry exceeds the guard's alpha (an interpolated alpha never exceeds both
-        // of its entries) or that light_kd <= 0.01
-        if (SHADE && c.w > a.shade_alpha) {  // GPURenderer4.cu:78 guard, :41-51 shade_texture
-            const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
-            const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
-            const float inv = fdiv(1.0f, __fsqrt_rn(len2));
-            const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
-            const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
-            const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
-            const float diffuse = fmul(fsub(tri_fetch(t, g, qx, qy, qz), s), a.kd);
-            c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
-            if (COUNT) cnt.shaded++;
+        if (!(ZS && __float_as_uint(tpm) < t.zero_um)) {
+            float4 c = tri_classify_at(g.pair_c, tpos, tpm);
+            // SHADE=false: the host has seen that no TF entry exceeds the guard's alpha (an interpolated alpha never exceeds both
+            // of its entries) or that light_kd <= 0.01
+            if (SHADE && c.w > a.shade_alpha) {  // GPURenderer4.cu:78 guard, :41-51 shade_texture
+                const float lvx = fsub(a.lx, px), lvy = fsub(a.ly, py), lvz = fsub(a.lz, pz);
+                const float len2 = fadd(fadd(fmul(lvx, lvx), fmul(lvy, lvy)), fmul(lvz, lvz));
+                const float inv = fdiv(1.0f, __fsqrt_rn(len2));
+                const float qx = fadd(px, fmul(fmul(lvx, inv), 0.01f));
+                const float qy = fadd(py, fmul(fmul(lvy, inv), 0.01f));
+                const float qz = fadd(pz, fmul(fmul(lvz, inv), 0.01f));
+                const float diffuse = fmul(fsub(tri_fetch(t, g, qx, qy, qz), s), a.kd);
+                c.x = fadd(c.x, diffuse); c.y = fadd(c.y, diffuse); c.z = fadd(c.z, diffuse);
+                if (COUNT) cnt.shaded++;
+            }
+            const float tr = fsub(1.0f, aa);
+            ar = fadd(ar, fmul(c.x, tr)); ag = fadd(ag, fmul(c.y, tr)); ab = fadd(ab, fmul(c.z, tr)); aa = fadd(aa, fmul(c.w, tr));
+            if (aa > g.threshold) break;
         }
-        const float tr = fsub(1.0f, aa);
-        ar = fadd(ar, fmul(c.x, tr)); ag = fadd(ag, fmul(c.y, tr)); ab = fadd(ab, fmul(c.z, tr)); aa = fadd(aa, fmul(c.w, tr));
-        if (aa > g.threshold) break;
         k = kn; px = nx; py = ny; pz = nz; tap = next;
     }
     return trunc_clamp(fmul(ar, 256.0f), 255u) | (trunc_clamp(fmul(ag, 256.0f), 255u) << 8) |
@@ -373,7 +390,7 @@ __device__ __forceinline__ uint32_t cast_ray_tri(const KArgs &a, const RayView &
 // same persistent-warp / tile-queue skeleton as cast_kernel
 // MINB = resident CTAs per SM the register budget is cut for (0: none; 6 = 40 registers, 5 = 48, 4 = 64); DEPTH = cell
 // requests in flight per ray (contracted march only)
-template <bool COUNT, bool FAST, bool SHADE, bool FMA, int MINB = (SHADE ? 0 : 6), int DEPTH = 1>
+template <bool COUNT, bool FAST, bool SHADE, bool FMA, int MINB = (SHADE ? 0 : 6), int DEPTH = 1, bool ZS = false>
 __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_constant__ KArgs a, const __grid_constant__ TriArgs t) {
     __shared__ float4 s_pair[2][kTriPairs];  // [0]: entries, [1]: differences to the next entry
     __shared__ uint32_t s_esl[1024];
@@ -399,7 +416,7 @@ __global__ void __launch_bounds__(kCtaThreads, MINB) tri_kernel(const __grid_con
 #endif
     Counters cnt = {0, 0, 0, 0, 0};
     run_tile_queue<COUNT>(a, [&](const RayView &v, int col, int row) {
-        return cast_ray_tri<COUNT, FAST, SHADE, FMA, DEPTH>(a, v, t, g, s_esl, &s_esl_pin, col, row, cnt);
+        return cast_ray_tri<COUNT, FAST, SHADE, FMA, DEPTH, ZS>(a, v, t, g, s_esl, &s_esl_pin, col, row, cnt);
     });
     if (COUNT) {
         unsigned long long v[5] = {cnt.rays_hit, cnt.rays_accum, cnt.esl_iters, cnt.samples, cnt.shaded};
