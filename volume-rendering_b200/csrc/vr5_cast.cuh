@@ -17,8 +17,14 @@ namespace vr5 {
 constexpr int kCtaThreads = 256;  // 8 warps; each warp owns one 8x4 pixel tile at a time
 constexpr int kTileW = 8;
 constexpr int kTileH = 4;         // = strip height of the multi-GPU partition
-constexpr int kGroupLog2X = 2;    // default queue order: groups of 4x8 tiles (32x32 px) so neighbouring queue slots
-constexpr int kGroupLog2Y = 3;    //                      touch neighbouring voxels (L1/L2 locality)
+#ifndef VR5_GROUP_LOG2X
+#define VR5_GROUP_LOG2X 2
+#endif
+#ifndef VR5_GROUP_LOG2Y
+#define VR5_GROUP_LOG2Y 3
+#endif
+constexpr int kGroupLog2X = VR5_GROUP_LOG2X;    // default queue order: groups of 4x8 tiles (32x32 px) so neighbouring queue slots
+constexpr int kGroupLog2Y = VR5_GROUP_LOG2Y;    //                      touch neighbouring voxels (L1/L2 locality)
 // Software-pipeline depth of the march loop: the voxel of sample i + kPrefetch is requested before sample i is composited
 // (1 or 2; the launcher bounds the speculative reach with it, reach_ok() in vr5_render.cu). Depth 2 - two slots in an unrolled
 // loop, no register moves, 55 instead of 54 instructions per pair of samples, bit-identical frames - measured SLOWER on B200:
