@@ -7,6 +7,11 @@
 // and square root are the correctly rounded variants, denormals are kept (-ftz=false), min/max are the reference's
 // ternaries (common.h:93-101), float->index is truncation (common.h:105-110). Integer index arithmetic is free to
 // differ (layouts, 64-bit offsets) because it is exact.
+//
+// Two shortcuts leave work out WITHOUT touching that rule (both only when the host has seen an all-zero prefix in the transfer
+// function, cast_ray<.., ZS>): a sample that classifies to an all-zero entry skips the compositing it cannot change, and runs of
+// such samples inside bricks that hold nothing else are leapt over, landing on the ray parameter the reference's sequential
+// k += step would hold (try_leap). The pixels stay the reference's, bit for bit (tests/test_zero_skip.py, tests/test_leap.py).
 #pragma once
 
 #include <cuda_runtime.h>
