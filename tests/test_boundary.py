@@ -137,3 +137,16 @@ def test_constant_increment_of_the_ray_parameter(tmp_path):
     subprocess.run(["gcc", "-O2", "-ffp-contract=off", os.path.join(ROOT, "tools", "check_kleap.c"), "-o", str(exe), "-lm"], check=True)
     out = subprocess.run([str(exe), "20000"], check=True, capture_output=True, text=True).stdout
     assert "mismatches 0" in out and "steps compared 0" not in out, out
+
+
+def test_leap_geometry_against_the_reference_arithmetic(tmp_path):
+    """tools/check_leap_geometry.c replays the leap rule of the zero-skip kernels (brick look-up, shrunk exit times, brick-to-brick walk
+    over clean crossings, floor(t / inc), binade cap) on random and adversarial rays and checks that every sample a leap leaves out
+    reads, in the reference's own fp32 arithmetic (ModelBase.h:17-23 on origin + direction * k), a voxel of a brick the walk accepted,
+    and that the ray parameter after the leap is the reference's. Without the margin the same check must FIND violations."""
+    exe = tmp_path / "check_leap_geometry"
+    subprocess.run(["gcc", "-O1", "-ffp-contract=off", os.path.join(ROOT, "tools", "check_leap_geometry.c"), "-o", str(exe), "-lm"], check=True)
+    out = subprocess.run([str(exe), "150000"], check=True, capture_output=True, text=True).stdout
+    assert "violations 0 " in out and "leaps 0," not in out, out
+    bad = subprocess.run([str(exe), "150000"], capture_output=True, text=True, env=dict(os.environ, CLG_MARGIN_SCALE="0"))
+    assert bad.returncode != 0 and "VOXEL VIOLATION" in bad.stdout, bad.stdout[-500:]
