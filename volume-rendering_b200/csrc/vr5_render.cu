@@ -1154,7 +1154,8 @@ int vr5_sequence_launch(vr5_renderer *r, const vr5_params *frames, int n, const 
             KArgs ai;   // the unclamped variants must hold for every frame: carry the largest reach
             if (fill_args(r, &p, targets[i].out_dev, &ai)) return 1;
             a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
-            if (!ai.brick_max) a.brick_max = nullptr;   // ... and so must the position bound of the leaps
+            if (!ai.brick_max) a.brick_max = nullptr;   // ... and so must the position bound of the leaps, with the widest margin any frame asks for
+            else if (ai.leap_margin > a.leap_margin) a.leap_margin = ai.leap_margin;
             band0 = (uint32_t)ai.rank; bandn = ai.tile_rows_local;
             if (bandn > max_rows) max_rows = bandn;
         }
@@ -1254,7 +1255,8 @@ extern "C" int vr5_render_sequence_noalloc(vr5_renderer *r, const vr5_params *fr
             KArgs ai;
             if (fill_args(r, &p, outs_dev[i], &ai)) return 1;
             a.reach = ai.reach > a.reach || !(ai.reach == ai.reach) ? ai.reach : a.reach;
-            if (!ai.brick_max) a.brick_max = nullptr;   // ... and so must the position bound of the leaps
+            if (!ai.brick_max) a.brick_max = nullptr;   // ... and so must the position bound of the leaps, with the widest margin any frame asks for
+            else if (ai.leap_margin > a.leap_margin) a.leap_margin = ai.leap_margin;
             band0 = (uint32_t)ai.rank; bandn = ai.tile_rows_local;
             if (bandn > max_rows) max_rows = bandn;
         }
